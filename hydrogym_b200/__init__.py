@@ -1,0 +1,12 @@
+"""hydrogym_b200 -- B200-native drop-in for the hydrogym/jax Kolmogorov-flow environment step.
+
+Only the hot path named in BASELINE.json is implemented; the compute
+runs in hand-written sm_100a CUDA kernels behind the C ABI of ``include/kolmo_b200.h``.
+"""
+from .envs.kolmogorov import (FlowConfig, KolmogorovFlow, KolmogorovFlowParams,  # noqa: F401
+                              KolmogorovFlowState)
+from .solver import KolmogorovStepper  # noqa: F401
+from .vector_env import KolmogorovVectorEnv  # noqa: F401
+
+__all__ = ["FlowConfig", "KolmogorovFlow", "KolmogorovFlowParams", "KolmogorovFlowState",
+           "KolmogorovStepper", "KolmogorovVectorEnv"]

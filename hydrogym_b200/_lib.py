@@ -1,0 +1,73 @@
+"""ctypes binding of ``libkolmo_b200.so`` (C ABI declared in ``include/kolmo_b200.h``).
+
+There is no CPU fallback: if the shared library is missing, loading raises, and
+if no B200 is present ``kf_create`` fails -- both surface as exceptions.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libkolmo_b200.so")
+
+KF_F32, KF_F64 = 0, 1
+
+# every symbol include/kolmo_b200.h declares
+SYMBOLS = (
+    "kf_last_error", "kf_create", "kf_destroy", "kf_set_constants", "kf_rollout", "kf_rk_steps",
+    "kf_reward_obs", "kf_step", "kf_step_host", "kf_launch_count", "kf_workspace_bytes", "kf_chunk",
+)
+
+
+class KfConfig(ctypes.Structure):
+    _fields_ = [
+        ("N", ctypes.c_int), ("M", ctypes.c_int), ("B", ctypes.c_int), ("dtype", ctypes.c_int),
+        ("nu", ctypes.c_double), ("dt", ctypes.c_double),
+        ("n_inner", ctypes.c_int), ("n_outer", ctypes.c_int), ("dealias", ctypes.c_int),
+        ("drag", ctypes.c_double), ("device", ctypes.c_int), ("obs_size", ctypes.c_int),
+        ("min_action", ctypes.c_double), ("max_action", ctypes.c_double),
+        ("chunk", ctypes.c_int), ("use_graph", ctypes.c_int),
+    ]
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library once; raise if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(hydrogym_b200 has no CPU fallback)")
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, ip = ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)
+    lib.kf_last_error.restype = ctypes.c_char_p
+    lib.kf_last_error.argtypes = []
+    lib.kf_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(KfConfig)]
+    lib.kf_destroy.argtypes = [vp]
+    lib.kf_set_constants.argtypes = [vp, vp, vp]
+    lib.kf_rollout.argtypes = [vp, vp, vp, vp, vp]
+    lib.kf_rk_steps.argtypes = [vp, vp, vp, ctypes.c_int, vp]
+    lib.kf_reward_obs.argtypes = [vp, vp, ctypes.c_int, vp, vp, vp, vp]
+    lib.kf_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.kf_step_host.argtypes = [vp, vp, vp, vp, vp, vp]
+    for name in ("kf_create", "kf_destroy", "kf_set_constants", "kf_rollout", "kf_rk_steps", "kf_reward_obs",
+                 "kf_step", "kf_step_host", "kf_chunk"):
+        getattr(lib, name).restype = ctypes.c_int
+    lib.kf_launch_count.argtypes = [vp]
+    lib.kf_launch_count.restype = ctypes.c_longlong
+    lib.kf_workspace_bytes.argtypes = [vp]
+    lib.kf_workspace_bytes.restype = ctypes.c_size_t
+    lib.kf_chunk.argtypes = [vp]
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().kf_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"{what} failed: {msg}")

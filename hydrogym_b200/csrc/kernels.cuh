@@ -1,0 +1,413 @@
+// Fused kernels of one IMEX Runge-Kutta sub-stage of the Kolmogorov-flow solve.
+//
+// Reference path: RK4_CN.time_step_fn (hydrogym/jax/solvers/base.py:50-57) calling
+// PseudoSpectralNavierStokes2D.nonlinear_terms / linear_terms / implicit_timestep
+// (hydrogym/jax/envs/kolmogorov.py:209-257).  One sub-stage is two launches:
+//
+//   col_kernel : forward x-FFT of the advection rows -> + forcing/control on row
+//                kx=0 -> h, omega_hat update (RK accumulate + Crank-Nicolson solve)
+//                -> u_hat, v_hat, d/dx, d/dy of the NEW omega_hat -> inverse x-FFT
+//   row_kernel : c2r y-FFT of the 4 fields -> -(gx*u + gy*v) -> r2c y-FFT
+//
+// Layouts (per environment):
+//   spectral  omega_hat, h : main[N][M/2] (ky = 0..M/2-1) + nyq[N] (ky = M/2)
+//   x-space   fields, adv  : [N][M/2] complex with column 0 PACKED as
+//             Re(column ky=0) + i*Re(column ky=M/2): irfftn drops the imaginary
+//             part of those two columns after the x-transform, and rfftn's y-pass
+//             makes them real, so one complex column carries both.
+// Wavenumbers are the integers p = fftfreq index, q = rfftfreq index (2*pi*kx = p).
+#pragma once
+#include "fft.cuh"
+
+namespace kf {
+
+template <typename T> struct StageArgs {
+  Cx<T>* wmain;        // [Bc][N][M/2]
+  Cx<T>* wnyq;         // [Bc][N]
+  Cx<T>* hmain;        // [Bc][N][M/2]
+  Cx<T>* hnyq;         // [Bc][N]
+  const Cx<T>* G;      // [Bc][M/2+1]  forcing + control row (kx = 0)
+  Cx<T>* advx;         // [Bc][N][M/2] packed x-space advection
+  Cx<T>* fld;          // [4][Bc][N][M/2] packed x-space u, v, gx, gy
+  size_t fstride;      // elements between fields
+  const Cx<T>* tw;     // [N] exp(-2*pi*i*m/N)
+  T beta, gdt, munu;   // beta_s, gamma_s*dt, mu_s*nu
+  T scale;             // 1/(N*M), folded into the prologue
+  int do_epi, do_pro, dealias, nfld;
+};
+
+// exchange policy of the column kernel: TC columns interleaved, conflict-free
+template <typename T, int TC> struct ColEx {
+  Cx<T>* sm; int c;
+  __device__ __forceinline__ void store(int pos, Cx<T> a) { stc(sm + pos * TC + c, a); }
+  __device__ __forceinline__ Cx<T> load(int pos) { return ldc(sm + pos * TC + c); }
+  __device__ __forceinline__ void sync() { __syncthreads(); }
+};
+
+// exchange policy of the row kernels: one padded buffer per FFT group
+template <typename T, int TPF> struct RowEx {
+  Cx<T>* sm;
+  __device__ __forceinline__ static int pad(int pos) { return pos + (pos >> 4); }
+  __device__ __forceinline__ void store(int pos, Cx<T> a) { stc(sm + pad(pos), a); }
+  __device__ __forceinline__ Cx<T> load(int pos) { return ldc(sm + pad(pos)); }
+  __device__ __forceinline__ void sync() {
+    if (TPF <= 32) __syncwarp(); else __syncthreads();
+  }
+};
+
+template <int N> __device__ __forceinline__ int wavenum(int i) { return i < N / 2 ? i : i - N; }
+
+// real coefficient c such that field_hat = c * (i * omega_hat); f: 0 u, 1 v, 2 gx, 3 gy
+template <typename T> __device__ __forceinline__ T field_coef(int f, T p, T q, T scale) {
+  const T k2 = p * p + q * q;
+  const T ik2 = k2 > (T)0 ? scale / k2 : (T)0;
+  return f == 0 ? q * ik2 : f == 1 ? -p * ik2 : f == 2 ? p * scale : q * scale;
+}
+
+// ---------------------------------------------------------------------------
+// Column kernel.  grid = (M/2 / TC, Bc), block = TPF*TC threads; thread (c, t)
+// owns column q = tile*TC + c and rows {t + TPF*m}: every global access is a run
+// of TC consecutive complex numbers per row (128 B for TC=16 complex64).
+// Tile 0 also carries the ky = M/2 column, packed with ky = 0 in x-space.
+// ---------------------------------------------------------------------------
+template <typename T, class P, int TC>
+__global__ void __launch_bounds__(P::TPF* TC) col_kernel(StageArgs<T> a) {
+  constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw);
+  Cx<T>* s_nyq = s_tw + N;
+  Cx<T>* s_ex = s_nyq + N;
+  const int c = threadIdx.x % TC, t = threadIdx.x / TC;
+  const int b = blockIdx.y;
+  const int q = blockIdx.x * TC + c;
+  const bool special = (blockIdx.x == 0);  // CTA-uniform
+  const T qf = (T)q;
+  const size_t plane = (size_t)N * MH;
+  Cx<T>* wmain = a.wmain + b * plane;
+  Cx<T>* wnyq = a.wnyq + (size_t)b * N;
+
+  for (int i = threadIdx.x; i < N; i += TPF * TC) s_tw[i] = ldc(a.tw + i);
+  __syncthreads();
+
+  ColEx<T, TC> ex{s_ex, c};
+  Cx<T> w[E];
+
+  if (a.do_epi) {
+    Cx<T>* hmain = a.hmain + b * plane;
+    Cx<T>* hnyq = a.hnyq + (size_t)b * N;
+    const Cx<T>* G = a.G + (size_t)b * (MH + 1);
+    const Cx<T>* advx = a.advx + b * plane;
+    const bool use_h = (a.beta != (T)0);
+    Cx<T> v[E];
+#pragma unroll
+    for (int m = 0; m < E; ++m) v[m] = ldc(advx + (size_t)(t + TPF * m) * MH + q);
+    fft_regs<P, -1, T>(v, s_tw, t, ex);
+
+    if (special) {
+      // unpack column 0: A0[kx] = (W[kx] + conj(W[-kx]))/2, An[kx] = (W[kx] - conj(W[-kx]))/(2i)
+      if (c == 0) {
+#pragma unroll
+        for (int m = 0; m < E; ++m) stc(s_ex + t + TPF * m, v[m]);
+      }
+      __syncthreads();
+      if (c == 0) {
+#pragma unroll
+        for (int m = 0; m < E; ++m) {
+          const int kx = t + TPF * m;
+          const Cx<T> wm = conj(ldc(s_ex + ((N - kx) & (N - 1))));
+          const Cx<T> d = v[m] - wm;
+          v[m] = (T)0.5 * (v[m] + wm);
+          Cx<T> nl = mk<T>((T)0.5 * d.y, (T)-0.5 * d.x);
+          if (a.dealias) nl = mk<T>((T)0, (T)0);  // ky = M/2 >= km always
+          if (kx == 0) nl = nl + ldc(G + MH);
+          Cx<T> h = nl;
+          if (use_h) h = h + a.beta * ldc(hnyq + kx);
+          stc(hnyq + kx, h);
+          const T p = (T)wavenum<N>(kx);
+          const T lk = a.munu * (p * p + (T)MH * (T)MH);
+          Cx<T> wv = ldc(wnyq + kx);
+          wv = ((T)1 / ((T)1 + lk)) * (wv + a.gdt * h - lk * wv);
+          stc(wnyq + kx, wv);
+          stc(s_nyq + kx, wv);
+        }
+      }
+      __syncthreads();
+    }
+
+    const int kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3;
+#pragma unroll
+    for (int m = 0; m < E; ++m) {
+      const int kx = t + TPF * m;
+      const size_t off = (size_t)kx * MH + q;
+      Cx<T> nl = v[m];
+      if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) nl = mk<T>((T)0, (T)0);
+      if (kx == 0) nl = nl + ldc(G + q);
+      Cx<T> h = nl;
+      if (use_h) h = h + a.beta * ldc(hmain + off);
+      stc(hmain + off, h);
+      const T p = (T)wavenum<N>(kx);
+      const T lk = a.munu * (p * p + qf * qf);
+      const Cx<T> wv = ldc(wmain + off);
+      w[m] = ((T)1 / ((T)1 + lk)) * (wv + a.gdt * h - lk * wv);
+      stc(wmain + off, w[m]);
+    }
+  } else {
+#pragma unroll
+    for (int m = 0; m < E; ++m) w[m] = ldc(wmain + (size_t)(t + TPF * m) * MH + q);
+    if (special) {
+      for (int i = threadIdx.x; i < N; i += TPF * TC) s_nyq[i] = ldc(wnyq + i);
+      __syncthreads();
+    }
+  }
+
+  if (a.do_pro) {
+#pragma unroll 1
+    for (int f = 0; f < a.nfld; ++f) {
+      Cx<T> v[E];
+#pragma unroll
+      for (int m = 0; m < E; ++m) {
+        const T p = (T)wavenum<N>(t + TPF * m);
+        v[m] = field_coef<T>(f, p, qf, a.scale) * mul_i(w[m]);
+      }
+      if (special) {
+        // column 0 <- herm(field[:,0]) + i*herm(field[:,M/2]); herm(a)[kx] = (a[kx]+conj(a[-kx]))/2
+        Cx<T>* sA = s_ex;
+        Cx<T>* sB = s_ex + N;
+        if (c == 0) {
+#pragma unroll
+          for (int m = 0; m < E; ++m) {
+            const int kx = t + TPF * m;
+            const T p = (T)wavenum<N>(kx);
+            stc(sA + kx, v[m]);
+            stc(sB + kx, field_coef<T>(f, p, (T)MH, a.scale) * mul_i(ldc(s_nyq + kx)));
+          }
+        }
+        __syncthreads();
+        if (c == 0) {
+#pragma unroll
+          for (int m = 0; m < E; ++m) {
+            const int kx = t + TPF * m;
+            const int mkx = (N - kx) & (N - 1);
+            const Cx<T> ah = (T)0.5 * (v[m] + conj(ldc(sA + mkx)));
+            const Cx<T> bh = (T)0.5 * (ldc(sB + kx) + conj(ldc(sB + mkx)));
+            v[m] = mk<T>(ah.x - bh.y, ah.y + bh.x);
+          }
+        }
+        __syncthreads();
+      }
+      fft_regs<P, +1, T>(v, s_tw, t, ex);
+      Cx<T>* out = a.fld + f * a.fstride + b * plane;
+#pragma unroll
+      for (int m = 0; m < E; ++m) stc(out + (size_t)(t + TPF * m) * MH + q, v[m]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Row kernels.  A group of TPF threads owns two x-rows (x0, x0+1).  Per row, two
+// complex length-M inverse FFTs give (u + i v) and (gx + i gy) -- two real c2r
+// transforms per complex FFT -- and the two rows' advection values go through
+// ONE forward complex FFT, W = FFT(adv[x0] + i adv[x0+1]), split afterwards by
+// Hermitian symmetry.  Global loads are direct (coalesced both for k and for the
+// mirrored index M-k); the only shared-memory traffic is the FFT exchange.
+// ---------------------------------------------------------------------------
+
+// Z[k] = A[k] + i B[k] for the Hermitian extensions of the packed half-rows A, B
+template <typename T, class P>
+__device__ __forceinline__ void load_pair_hermitian(Cx<T>* z, const Cx<T>* __restrict__ A,
+                                                    const Cx<T>* __restrict__ B, int t) {
+  constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF;
+#pragma unroll
+  for (int m = 0; m < E; ++m) {
+    const int k = t + TPF * m;
+    if (m < E / 2) {
+      const Cx<T> a = ldc(A + k), b = ldc(B + k);
+      z[m] = (k == 0) ? mk<T>(a.x, b.x) : mk<T>(a.x - b.y, a.y + b.x);
+    } else {
+      const int src = (k == MH) ? 0 : M - k;
+      const Cx<T> a = ldc(A + src), b = ldc(B + src);
+      z[m] = (k == MH) ? mk<T>(a.y, b.y) : mk<T>(a.x + b.y, b.x - a.y);
+    }
+  }
+}
+
+template <typename T, class P, int GROUPS>
+__global__ void __launch_bounds__(P::TPF* GROUPS) row_kernel(StageArgs<T> a) {
+  constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF, N = M;
+  constexpr int EXN = M + M / 16;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw);
+  const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
+  RowEx<T, TPF> ex{s_tw + M + g * EXN};
+  const int b = blockIdx.y;
+  const int x0 = 2 * (blockIdx.x * GROUPS + g);
+  const size_t plane = (size_t)N * MH;
+
+  for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
+  __syncthreads();
+
+  T adv[2][E];
+#pragma unroll
+  for (int rr = 0; rr < 2; ++rr) {
+    const size_t roff = b * plane + (size_t)(x0 + rr) * MH;
+    Cx<T> z1[E], z2[E];
+    load_pair_hermitian<T, P>(z1, a.fld + roff, a.fld + a.fstride + roff, t);
+    fft_regs<P, +1, T>(z1, s_tw, t, ex);
+    load_pair_hermitian<T, P>(z2, a.fld + 2 * a.fstride + roff, a.fld + 3 * a.fstride + roff, t);
+    fft_regs<P, +1, T>(z2, s_tw, t, ex);
+#pragma unroll
+    for (int m = 0; m < E; ++m) adv[rr][m] = -(z2[m].x * z1[m].x + z2[m].y * z1[m].y);
+  }
+
+  Cx<T> v[E];
+#pragma unroll
+  for (int m = 0; m < E; ++m) v[m] = mk<T>(adv[0][m], adv[1][m]);
+  fft_regs<P, -1, T>(v, s_tw, t, ex);
+#pragma unroll
+  for (int m = 0; m < E; ++m) ex.store(t + TPF * m, v[m]);
+  ex.sync();
+  Cx<T>* o0 = a.advx + b * plane + (size_t)x0 * MH;
+  Cx<T>* o1 = o0 + MH;
+#pragma unroll
+  for (int m = 0; m < E / 2; ++m) {
+    const int k = t + TPF * m;
+    if (k == 0) {
+      const Cx<T> wn = ex.load(MH);
+      stc(o0, mk<T>(v[m].x, wn.x));
+      stc(o1, mk<T>(v[m].y, wn.y));
+    } else {
+      const Cx<T> wm = conj(ex.load(M - k));
+      const Cx<T> d = v[m] - wm;
+      stc(o0 + k, (T)0.5 * (v[m] + wm));
+      stc(o1 + k, mk<T>((T)0.5 * d.y, (T)-0.5 * d.x));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Reward / observation row kernel (reference: compute_tke utils.py:175-194 and
+// _trajectory_mean_obs kolmogorov.py:426-446).  Consumes the x-space u_hat, v_hat
+// fields of one snapshot; per environment accumulates sum u, sum v, sum u^2,
+// sum v^2 (fp64, warp-shuffle reduction + one atomic per warp) and adds
+// |velocity| at the obs_size x obs_size strided probes into the running obs mean.
+// ---------------------------------------------------------------------------
+template <typename T> struct ObsArgs {
+  const Cx<T>* fld;    // [2][Bc][N][M/2]
+  size_t fstride;
+  const Cx<T>* tw;
+  double* acc;         // [Bc][4] for this snapshot (stride acc_stride between envs)
+  size_t acc_stride;
+  T* obs;              // [Bc][nobs*nobs], accumulated with weight obs_w
+  int nobs, sx, sy;
+  T obs_w;
+};
+
+template <typename T, class P, int GROUPS>
+__global__ void __launch_bounds__(P::TPF* GROUPS) row_obs_kernel(ObsArgs<T> a) {
+  constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF, N = M;
+  constexpr int EXN = M + M / 16;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw);
+  const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
+  RowEx<T, TPF> ex{s_tw + M + g * EXN};
+  const int b = blockIdx.y;
+  const int x = blockIdx.x * GROUPS + g;
+  const size_t roff = ((size_t)b * N + x) * MH;
+
+  for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
+  __syncthreads();
+
+  Cx<T> z[E];
+  load_pair_hermitian<T, P>(z, a.fld + roff, a.fld + a.fstride + roff, t);
+  fft_regs<P, +1, T>(z, s_tw, t, ex);
+
+  T su = 0, sv = 0, suu = 0, svv = 0;
+#pragma unroll
+  for (int m = 0; m < E; ++m) {
+    su += z[m].x; sv += z[m].y;
+    suu += z[m].x * z[m].x; svv += z[m].y * z[m].y;
+  }
+  if (x % a.sx == 0 && x / a.sx < a.nobs) {
+#pragma unroll
+    for (int m = 0; m < E; ++m) {
+      const int y = t + TPF * m;
+      if (y % a.sy == 0 && y / a.sy < a.nobs) {
+        T* o = a.obs + (size_t)b * a.nobs * a.nobs + (x / a.sx) * a.nobs + y / a.sy;
+        *o += a.obs_w * sqrt(z[m].x * z[m].x + z[m].y * z[m].y);  // single writer per launch
+      }
+    }
+  }
+  double r[4] = {(double)su, (double)sv, (double)suu, (double)svv};
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r[i] += __shfl_xor_sync(0xffffffffu, r[i], off);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    double* acc = a.acc + (size_t)b * a.acc_stride;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) atomicAdd(acc + i, r[i]);
+  }
+}
+
+// mean_tke[b] = mean_j 0.5*(sum((u-U)^2) + sum((v-V)^2))/n^2 ; nonfinite flag
+template <typename T>
+__global__ void tke_finalize_kernel(const double* acc, int B, int nsnap, int N, int M, T* mean_tke, int* nonfinite) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const double cnt = (double)N * (double)M;
+  double s = 0.0;
+  for (int j = 0; j < nsnap; ++j) {
+    const double* r = acc + ((size_t)b * nsnap + j) * 4;
+    s += 0.5 * ((r[2] - r[0] * r[0] / cnt) + (r[3] - r[1] * r[1] / cnt)) / ((double)N * (double)N);
+  }
+  s /= (double)nsnap;
+  if (mean_tke) mean_tke[b] = (T)s;
+  if (nonfinite) nonfinite[b] = isfinite(s) ? 0 : 1;
+}
+
+// ---------------------------------------------------------------------------
+// Layout conversion and the per-step forcing row.
+// ---------------------------------------------------------------------------
+// user omega_hat [B][N][M/2+1] (row stride = user_row, env stride = user_env) <-> internal
+template <typename T>
+__global__ void import_kernel(const Cx<T>* __restrict__ user, size_t user_env, Cx<T>* main, Cx<T>* nyq, int N, int MH) {
+  const int b = blockIdx.y;
+  const int total = N * (MH + 1);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int kx = i / (MH + 1), q = i - kx * (MH + 1);
+    const Cx<T> v = ldc(user + (size_t)b * user_env + i);
+    if (q == MH) stc(nyq + (size_t)b * N + kx, v);
+    else stc(main + ((size_t)b * N + kx) * MH + q, v);
+  }
+}
+template <typename T>
+__global__ void export_kernel(Cx<T>* __restrict__ user, size_t user_env, const Cx<T>* main, const Cx<T>* nyq, int N, int MH) {
+  const int b = blockIdx.y;
+  const int total = N * (MH + 1);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int kx = i / (MH + 1), q = i - kx * (MH + 1);
+    const Cx<T> v = (q == MH) ? ldc(nyq + (size_t)b * N + kx) : ldc(main + ((size_t)b * N + kx) * MH + q);
+    stc(user + (size_t)b * user_env + i, v);
+  }
+}
+
+// G[b][q] = F[q] + sum_m clip(a[b][m]) * C[m][q]   (kolmogorov.py:386-395, 259-272, 274-292, env_core.py:419-420)
+template <typename T>
+__global__ void forcing_row_kernel(Cx<T>* G, const Cx<T>* F, const Cx<T>* C, const T* actions, T lo, T hi, int MH1) {
+  const int b = blockIdx.y;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= MH1) return;
+  Cx<T> g = ldc(F + q);
+  if (actions) {
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+      T am = actions[(size_t)b * 4 + m];
+      am = am < lo ? lo : (am > hi ? hi : am);
+      g = g + am * ldc(C + (size_t)m * MH1 + q);
+    }
+  }
+  stc(G + (size_t)b * MH1 + q, g);
+}
+
+}  // namespace kf

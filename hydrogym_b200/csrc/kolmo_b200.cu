@@ -1,0 +1,516 @@
+// C-ABI implementation (include/kolmo_b200.h): workspace, launch sequencing,
+// CUDA-graph replay and chunked (L2-blocked) stepping.  sm_100a only.
+#include "../../include/kolmo_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(const std::string& msg) {
+  g_err = msg;
+  return 1;
+}
+
+#define KF_CUDA(expr)                                                                     \
+  do {                                                                                    \
+    cudaError_t e__ = (expr);                                                             \
+    if (e__ != cudaSuccess)                                                               \
+      return fail(std::string(#expr) + ": " + cudaGetErrorString(e__));                   \
+  } while (0)
+
+// reference coefficients, hydrogym/jax/solvers/base.py:13-15
+const double kAlpha[6] = {0, 0.1496590219993, 0.3704009573644, 0.6222557631345, 0.9582821306748, 1};
+const double kBeta[5] = {0, -0.4178904745, -1.192151694643, -1.697784692471, -1.514183444257};
+const double kGamma[5] = {0.1496590219993, 0.3792103129999, 0.8229550293869, 0.6994504559488, 0.1530572479681};
+
+struct Stage {  // type-erased per-stage scalars
+  double beta, gdt, munu;
+};
+
+// Type-erased launch table, one instance per (dtype, N).
+struct Ops {
+  size_t elem;  // bytes per complex
+  int tc, col_threads, row_groups, row_threads;
+  size_t col_smem, row_smem;
+  cudaError_t (*prepare)();
+  // all of these work on the chunk-local workspace; nb = environments in the chunk
+  void (*col)(const struct Ctx&, int nb, const Stage&, int do_epi, int do_pro, int nfld, cudaStream_t);
+  void (*row)(const struct Ctx&, int nb, cudaStream_t);
+  // obs_dev / acc already offset to the chunk's first environment
+  void (*obs)(const struct Ctx&, int nb, double* acc, size_t acc_stride, void* obs_dev, double obs_w, cudaStream_t);
+  void (*finalize)(const struct Ctx&, int nsnap, void* mean_tke, int* nonfinite, cudaStream_t);
+  void (*import_)(const struct Ctx&, int nb, const void* user, size_t user_env, cudaStream_t);
+  void (*export_)(const struct Ctx&, int nb, void* user, size_t user_env, cudaStream_t);
+  void (*forcing)(const struct Ctx&, int nb, const void* actions, cudaStream_t);
+};
+
+struct Ctx {
+  kf_config cfg;
+  const Ops* ops;
+  int N, MH, chunk;
+  size_t plane;  // complex elements per env of a main/x-space array
+  // device buffers (void*: complex<T>)
+  // chunk-local workspace
+  void *wmain = nullptr, *wnyq = nullptr, *hmain = nullptr, *hnyq = nullptr, *G = nullptr;
+  void *fld = nullptr, *advx = nullptr, *tw = nullptr, *F = nullptr, *C = nullptr;
+  double* acc = nullptr;  // [B][acc_snaps][4]
+  int acc_snaps = 0;
+  // device staging for kf_step_host (allocated on first use)
+  void *d_omega = nullptr, *d_act = nullptr, *d_obs = nullptr, *d_tke = nullptr;
+  int* d_nonf = nullptr;
+  size_t bytes = 0;
+  long long launches = 0;
+  bool have_constants = false;
+  // CUDA graph of `graph_steps` RK steps on a full chunk
+  cudaGraphExec_t graph = nullptr;
+  int graph_steps = 0;
+};
+
+
+template <typename T, class P, int TC, int GROUPS> struct Impl {
+  using C = kf::Cx<T>;
+  static constexpr int N = P::L, MH = N / 2;
+  static size_t col_smem() { return sizeof(C) * (2 * (size_t)N + (size_t)N * TC); }
+  static size_t row_smem() { return sizeof(C) * ((size_t)N + (size_t)GROUPS * (N + N / 16)); }
+
+  static cudaError_t prepare() {
+    cudaError_t e;
+    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kf::row_kernel<T, P, GROUPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem());
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(kf::row_obs_kernel<T, P, GROUPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)row_smem());
+  }
+
+  static kf::StageArgs<T> args(const Ctx& c) {
+    kf::StageArgs<T> a;
+    a.wmain = (C*)c.wmain; a.wnyq = (C*)c.wnyq; a.hmain = (C*)c.hmain; a.hnyq = (C*)c.hnyq;
+    a.G = (const C*)c.G; a.advx = (C*)c.advx; a.fld = (C*)c.fld;
+    a.fstride = (size_t)c.chunk * c.plane;
+    a.tw = (const C*)c.tw;
+    a.beta = 0; a.gdt = 0; a.munu = 0;
+    a.scale = (T)(1.0 / ((double)N * (double)N));
+    a.do_epi = 0; a.do_pro = 0; a.dealias = c.cfg.dealias; a.nfld = 4;
+    return a;
+  }
+
+  static void col(const Ctx& c, int nb, const Stage& st, int do_epi, int do_pro, int nfld, cudaStream_t s) {
+    kf::StageArgs<T> a = args(c);
+    a.beta = (T)st.beta; a.gdt = (T)st.gdt; a.munu = (T)st.munu;
+    a.do_epi = do_epi; a.do_pro = do_pro; a.nfld = nfld;
+    kf::col_kernel<T, P, TC><<<dim3(MH / TC, nb), P::TPF * TC, col_smem(), s>>>(a);
+  }
+  static void row(const Ctx& c, int nb, cudaStream_t s) {
+    kf::StageArgs<T> a = args(c);
+    kf::row_kernel<T, P, GROUPS><<<dim3(N / 2 / GROUPS, nb), P::TPF * GROUPS, row_smem(), s>>>(a);
+  }
+  static void obs(const Ctx& c, int nb, double* acc, size_t acc_stride, void* obs_dev, double obs_w, cudaStream_t s) {
+    kf::ObsArgs<T> a;
+    a.fld = (const C*)c.fld; a.fstride = (size_t)c.chunk * c.plane; a.tw = (const C*)c.tw;
+    a.acc = acc; a.acc_stride = acc_stride; a.obs = (T*)obs_dev;
+    a.nobs = obs_dev ? c.cfg.obs_size : 0;
+    a.sx = a.sy = N / c.cfg.obs_size;
+    a.obs_w = (T)obs_w;
+    kf::row_obs_kernel<T, P, GROUPS><<<dim3(N / GROUPS, nb), P::TPF * GROUPS, row_smem(), s>>>(a);
+  }
+  static void finalize(const Ctx& c, int nsnap, void* mean_tke, int* nonfinite, cudaStream_t s) {
+    const int B = c.cfg.B;
+    kf::tke_finalize_kernel<T><<<(B + 127) / 128, 128, 0, s>>>(c.acc, B, nsnap, N, N, (T*)mean_tke, nonfinite);
+  }
+  static void import_(const Ctx& c, int nb, const void* user, size_t user_env, cudaStream_t s) {
+    kf::import_kernel<T><<<dim3(32, nb), 256, 0, s>>>((const C*)user, user_env, (C*)c.wmain, (C*)c.wnyq, N, MH);
+  }
+  static void export_(const Ctx& c, int nb, void* user, size_t user_env, cudaStream_t s) {
+    kf::export_kernel<T><<<dim3(32, nb), 256, 0, s>>>((C*)user, user_env, (const C*)c.wmain, (const C*)c.wnyq, N, MH);
+  }
+  static void forcing(const Ctx& c, int nb, const void* actions, cudaStream_t s) {
+    kf::forcing_row_kernel<T><<<dim3((MH + 1 + 127) / 128, nb), 128, 0, s>>>(
+        (C*)c.G, (const C*)c.F, (const C*)c.C, (const T*)actions, (T)c.cfg.min_action, (T)c.cfg.max_action, MH + 1);
+  }
+  static Ops make() {
+    Ops o;
+    o.elem = sizeof(C);
+    o.tc = TC; o.col_threads = P::TPF * TC; o.row_groups = GROUPS; o.row_threads = P::TPF * GROUPS;
+    o.col_smem = col_smem(); o.row_smem = row_smem();
+    o.prepare = prepare; o.col = col; o.row = row; o.obs = obs; o.finalize = finalize;
+    o.import_ = import_; o.export_ = export_; o.forcing = forcing;
+    return o;
+  }
+};
+
+const Ops* find_ops(int dtype, int N) {
+  using kf::Plan;
+  static const Ops f64_[] = {Impl<float, Plan<64, 8, 8, 8>, 16, 16>::make()};
+  static const Ops f128[] = {Impl<float, Plan<128, 8, 16, 8>, 16, 16>::make()};
+  static const Ops f256[] = {Impl<float, Plan<256, 16, 16, 16>, 16, 8>::make()};
+  static const Ops f512[] = {Impl<float, Plan<512, 32, 8, 8, 8>, 8, 4>::make()};
+  static const Ops f1024[] = {Impl<float, Plan<1024, 64, 16, 4, 16>, 8, 2>::make()};
+  static const Ops d64[] = {Impl<double, Plan<64, 8, 8, 8>, 16, 16>::make()};
+  static const Ops d128[] = {Impl<double, Plan<128, 16, 8, 2, 8>, 8, 8>::make()};
+  static const Ops d256[] = {Impl<double, Plan<256, 32, 8, 4, 8>, 8, 4>::make()};
+  static const Ops d512[] = {Impl<double, Plan<512, 64, 8, 8, 8>, 4, 2>::make()};
+  static const Ops d1024[] = {Impl<double, Plan<1024, 128, 8, 2, 8, 8>, 4, 1>::make()};
+  const bool f = dtype == KF_F32;
+  switch (N) {
+    case 64: return f ? f64_ : d64;
+    case 128: return f ? f128 : d128;
+    case 256: return f ? f256 : d256;
+    case 512: return f ? f512 : d512;
+    case 1024: return f ? f1024 : d1024;
+    default: return nullptr;
+  }
+}
+
+}  // namespace
+
+namespace {
+
+Stage stage_of(const Ctx& c, int s) {
+  Stage st;
+  st.beta = kBeta[s];
+  st.gdt = kGamma[s] * c.cfg.dt;                                     // base.py:55
+  st.munu = 0.5 * c.cfg.dt * (kAlpha[s + 1] - kAlpha[s]) * c.cfg.nu;  // base.py:54, kolmogorov.py:209-220
+  return st;
+}
+
+// one RK solver step (5 sub-stages, 10 launches) on the chunk workspace;
+// expects the x-space fields of the current omega_hat to be present.
+void enqueue_rk_step(Ctx& c, int nb, cudaStream_t s) {
+  for (int k = 0; k < 5; ++k) {
+    c.ops->row(c, nb, s);
+    c.ops->col(c, nb, stage_of(c, k), 1, 1, 4, s);
+  }
+}
+
+int build_graph(Ctx& c) {
+  if (c.graph) return 0;
+  const int steps = 4;
+  cudaGraph_t g = nullptr;
+  // capture on a private stream (the caller's may be the legacy default stream, which cannot capture)
+  cudaStream_t cs = nullptr;
+  KF_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+  cudaError_t ce = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+  if (ce == cudaSuccess) {
+    for (int i = 0; i < steps; ++i) enqueue_rk_step(c, c.chunk, cs);
+    ce = cudaStreamEndCapture(cs, &g);
+  }
+  cudaStreamDestroy(cs);
+  if (ce != cudaSuccess) return fail(std::string("graph capture: ") + cudaGetErrorString(ce));
+  cudaError_t e = cudaGraphInstantiate(&c.graph, g, 0);
+  cudaGraphDestroy(g);
+  if (e != cudaSuccess) return fail(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
+  c.graph_steps = steps;
+  return 0;
+}
+
+// n RK steps on the chunk workspace (fields must be current on entry, are current on exit)
+int run_rk_steps(Ctx& c, int nb, int n, cudaStream_t s) {
+  int done = 0;
+  if (c.cfg.use_graph && nb == c.chunk && n >= 8) {
+    if (int rc = build_graph(c)) return rc;
+    while (n - done >= c.graph_steps) {
+      KF_CUDA(cudaGraphLaunch(c.graph, s));
+      done += c.graph_steps;
+      c.launches += 10LL * c.graph_steps;
+    }
+  }
+  for (; done < n; ++done) {
+    enqueue_rk_step(c, nb, s);
+    c.launches += 10;
+  }
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int ensure_acc(Ctx& c, int nsnap) {
+  if (nsnap <= c.acc_snaps) return 0;
+  if (c.acc) cudaFree(c.acc);
+  c.acc = nullptr;
+  KF_CUDA(cudaMalloc(&c.acc, sizeof(double) * 4 * (size_t)c.cfg.B * nsnap));
+  c.acc_snaps = nsnap;
+  return 0;
+}
+
+// Core driver shared by kf_rollout / kf_rk_steps / kf_step.
+//   n_outer blocks of n_inner RK steps; after each block: snapshot to trajectory
+//   (if given) and reward/obs reductions (if want_obs).
+int drive(Ctx& c, void* omega, const void* actions, void* traj, int n_outer, int n_inner, bool want_obs,
+          void* obs_dev, void* tke_dev, int* nonf_dev, cudaStream_t s) {
+  if (!c.have_constants) return fail("kf_set_constants has not been called");
+  const size_t el = c.ops->elem, real = el / 2;
+  const int B = c.cfg.B, N = c.N, MH1 = c.MH + 1;
+  const size_t user_env = (size_t)N * MH1;  // complex elements per env in user layout
+  const int nobs2 = c.cfg.obs_size * c.cfg.obs_size;
+  if (want_obs) {
+    if (int rc = ensure_acc(c, n_outer)) return rc;
+    KF_CUDA(cudaMemsetAsync(c.acc, 0, sizeof(double) * 4 * (size_t)B * n_outer, s));
+    if (obs_dev) KF_CUDA(cudaMemsetAsync(obs_dev, 0, real * (size_t)B * nobs2, s));
+  }
+  for (int b0 = 0; b0 < B; b0 += c.chunk) {
+    const int nb = (B - b0 < c.chunk) ? (B - b0) : c.chunk;
+    char* om = (char*)omega + el * user_env * b0;
+    c.ops->import_(c, nb, om, user_env, s);
+    c.ops->forcing(c, nb, actions ? (const char*)actions + real * 4 * b0 : nullptr, s);
+    c.ops->col(c, nb, stage_of(c, 0), 0, 1, 4, s);  // fields of the initial state
+    c.launches += 3;
+    for (int j = 0; j < n_outer; ++j) {
+      if (int rc = run_rk_steps(c, nb, n_inner, s)) return rc;
+      if (traj) {
+        char* tj = (char*)traj + el * user_env * ((size_t)b0 * n_outer + j);
+        c.ops->export_(c, nb, tj, user_env * n_outer, s);
+        c.launches += 1;
+      }
+      if (want_obs) {
+        c.ops->obs(c, nb, c.acc + 4 * ((size_t)b0 * n_outer + j), 4 * (size_t)n_outer,
+                   obs_dev ? (char*)obs_dev + real * (size_t)b0 * nobs2 : nullptr, 1.0 / n_outer, s);
+        c.launches += 1;
+      }
+    }
+    c.ops->export_(c, nb, om, user_env, s);
+    c.launches += 1;
+  }
+  if (want_obs) {
+    c.ops->finalize(c, n_outer, tke_dev, nonf_dev, s);
+    c.launches += 1;
+  }
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+struct kf_handle_s {
+  Ctx c;
+};
+
+namespace {
+
+int dev_alloc(Ctx& c, void** p, size_t bytes) {
+  KF_CUDA(cudaMalloc(p, bytes));
+  c.bytes += bytes;
+  return 0;
+}
+
+void free_all(Ctx& c) {
+  void* ptrs[] = {c.wmain, c.wnyq, c.hmain, c.hnyq, c.G, c.fld, c.advx, c.tw, c.F, c.C,
+                  c.acc, c.d_omega, c.d_act, c.d_obs, c.d_tke, c.d_nonf};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  if (c.graph) cudaGraphExecDestroy(c.graph);
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (prev >= 0 && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace
+
+extern "C" {
+
+const char* kf_last_error(void) { return g_err.c_str(); }
+
+int kf_create(kf_handle* out, const kf_config* cfg) {
+  if (!out || !cfg) return fail("kf_create: null argument");
+  *out = nullptr;
+  if (cfg->N != cfg->M) return fail("kf_create: only square grids are supported (N == M)");
+  if (cfg->dtype != KF_F32 && cfg->dtype != KF_F64) return fail("kf_create: dtype must be KF_F32 or KF_F64");
+  const Ops* ops = find_ops(cfg->dtype, cfg->N);
+  if (!ops) return fail("kf_create: grid size must be one of 64, 128, 256, 512, 1024");
+  if (cfg->B < 1) return fail("kf_create: B must be >= 1");
+  if (cfg->drag != 0.0) return fail("kf_create: drag must be 0 (the reference has no drag term)");
+  if (cfg->n_inner < 1 || cfg->n_outer < 1) return fail("kf_create: n_inner and n_outer must be >= 1");
+  if (cfg->obs_size < 1 || cfg->N % cfg->obs_size != 0) return fail("kf_create: obs_size must divide the grid size");
+  if (!(cfg->dt > 0.0) || !(cfg->nu >= 0.0)) return fail("kf_create: need dt > 0 and nu >= 0");
+  int ndev = 0;
+  KF_CUDA(cudaGetDeviceCount(&ndev));
+  if (cfg->device < 0 || cfg->device >= ndev) return fail("kf_create: no such CUDA device");
+  DeviceGuard guard(cfg->device);
+  cudaDeviceProp prop;
+  KF_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+  if (prop.major != 10) return fail("kf_create: this library is built for sm_100a (B200) only");
+
+  kf_handle h = new kf_handle_s();
+  Ctx& c = h->c;
+  c.cfg = *cfg;
+  c.ops = ops;
+  c.N = cfg->N;
+  c.MH = cfg->N / 2;
+  c.plane = (size_t)c.N * c.MH;
+  c.chunk = (cfg->chunk > 0 && cfg->chunk < cfg->B) ? cfg->chunk : cfg->B;
+  const size_t el = ops->elem;
+  const size_t cp = (size_t)c.chunk * c.plane;
+  int rc = 0;
+  cudaError_t pe = ops->prepare();
+  if (pe != cudaSuccess) rc = fail(std::string("kernel attribute setup: ") + cudaGetErrorString(pe));
+  if (!rc) rc = dev_alloc(c, &c.wmain, el * cp);
+  if (!rc) rc = dev_alloc(c, &c.hmain, el * cp);
+  if (!rc) rc = dev_alloc(c, &c.wnyq, el * (size_t)c.chunk * c.N);
+  if (!rc) rc = dev_alloc(c, &c.hnyq, el * (size_t)c.chunk * c.N);
+  if (!rc) rc = dev_alloc(c, &c.G, el * (size_t)c.chunk * (c.MH + 1));
+  if (!rc) rc = dev_alloc(c, &c.fld, el * 4 * cp);
+  if (!rc) rc = dev_alloc(c, &c.advx, el * cp);
+  if (!rc) rc = dev_alloc(c, &c.tw, el * c.N);
+  if (!rc) rc = dev_alloc(c, &c.F, el * (c.MH + 1));
+  if (!rc) rc = dev_alloc(c, &c.C, el * 4 * (c.MH + 1));
+  if (!rc) {
+    // twiddles exp(-2*pi*i*m/N), computed in fp64 and rounded once
+    std::vector<double> t64(2 * (size_t)c.N);
+    const double kPi = 3.14159265358979323846264338327950288;
+    for (int m = 0; m < c.N; ++m) {
+      t64[2 * m] = std::cos(2.0 * kPi * m / c.N);
+      t64[2 * m + 1] = -std::sin(2.0 * kPi * m / c.N);
+    }
+    cudaError_t e;
+    if (cfg->dtype == KF_F32) {
+      std::vector<float> t32(t64.begin(), t64.end());
+      e = cudaMemcpy(c.tw, t32.data(), el * c.N, cudaMemcpyHostToDevice);
+    } else {
+      e = cudaMemcpy(c.tw, t64.data(), el * c.N, cudaMemcpyHostToDevice);
+    }
+    if (e != cudaSuccess) rc = fail(std::string("twiddle upload: ") + cudaGetErrorString(e));
+  }
+  if (rc) {
+    free_all(c);
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return 0;
+}
+
+int kf_destroy(kf_handle h) {
+  if (!h) return 0;
+  DeviceGuard guard(h->c.cfg.device);
+  cudaDeviceSynchronize();
+  free_all(h->c);
+  delete h;
+  return 0;
+}
+
+int kf_set_constants(kf_handle h, const void* forcing_row, const void* control_rows) {
+  if (!h || !forcing_row || !control_rows) return fail("kf_set_constants: null argument");
+  Ctx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  const size_t row = c.ops->elem * (c.MH + 1);
+  KF_CUDA(cudaMemcpy(c.F, forcing_row, row, cudaMemcpyHostToDevice));
+  KF_CUDA(cudaMemcpy(c.C, control_rows, 4 * row, cudaMemcpyHostToDevice));
+  c.have_constants = true;
+  return 0;
+}
+
+int kf_rollout(kf_handle h, void* omega_hat_dev, const void* actions_dev, void* trajectory_dev, void* stream) {
+  if (!h || !omega_hat_dev) return fail("kf_rollout: null argument");
+  Ctx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  return drive(c, omega_hat_dev, actions_dev, trajectory_dev, c.cfg.n_outer, c.cfg.n_inner, false, nullptr, nullptr,
+               nullptr, (cudaStream_t)stream);
+}
+
+int kf_rk_steps(kf_handle h, void* omega_hat_dev, const void* actions_dev, int n_steps, void* stream) {
+  if (!h || !omega_hat_dev) return fail("kf_rk_steps: null argument");
+  if (n_steps < 0) return fail("kf_rk_steps: n_steps must be >= 0");
+  Ctx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  return drive(c, omega_hat_dev, actions_dev, nullptr, 1, n_steps, false, nullptr, nullptr, nullptr,
+               (cudaStream_t)stream);
+}
+
+int kf_step(kf_handle h, void* omega_hat_dev, const void* actions_dev, void* trajectory_dev, void* obs_dev,
+            void* mean_tke_dev, int* nonfinite_dev, void* stream) {
+  if (!h || !omega_hat_dev) return fail("kf_step: null argument");
+  Ctx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  return drive(c, omega_hat_dev, actions_dev, trajectory_dev, c.cfg.n_outer, c.cfg.n_inner, true, obs_dev,
+               mean_tke_dev, nonfinite_dev, (cudaStream_t)stream);
+}
+
+long long kf_launch_count(kf_handle h) { return h ? h->c.launches : 0; }
+size_t kf_workspace_bytes(kf_handle h) { return h ? h->c.bytes : 0; }
+int kf_chunk(kf_handle h) { return h ? h->c.chunk : 0; }
+
+}  // extern "C"
+
+extern "C" {
+
+int kf_reward_obs(kf_handle h, const void* trajectory_dev, int n_snap, void* obs_dev, void* mean_tke_dev,
+                  int* nonfinite_dev, void* stream) {
+  if (!h || !trajectory_dev) return fail("kf_reward_obs: null argument");
+  if (n_snap < 1) return fail("kf_reward_obs: n_snap must be >= 1");
+  Ctx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t el = c.ops->elem, real = el / 2;
+  const int B = c.cfg.B;
+  const size_t user_env = (size_t)c.N * (c.MH + 1);
+  const int nobs2 = c.cfg.obs_size * c.cfg.obs_size;
+  if (int rc = ensure_acc(c, n_snap)) return rc;
+  KF_CUDA(cudaMemsetAsync(c.acc, 0, sizeof(double) * 4 * (size_t)B * n_snap, s));
+  if (obs_dev) KF_CUDA(cudaMemsetAsync(obs_dev, 0, real * (size_t)B * nobs2, s));
+  for (int b0 = 0; b0 < B; b0 += c.chunk) {
+    const int nb = (B - b0 < c.chunk) ? (B - b0) : c.chunk;
+    for (int j = 0; j < n_snap; ++j) {
+      const char* tj = (const char*)trajectory_dev + el * user_env * ((size_t)b0 * n_snap + j);
+      c.ops->import_(c, nb, tj, user_env * n_snap, s);
+      c.ops->col(c, nb, stage_of(c, 0), 0, 1, 2, s);  // u_hat, v_hat -> x-space
+      c.ops->obs(c, nb, c.acc + 4 * ((size_t)b0 * n_snap + j), 4 * (size_t)n_snap,
+                 obs_dev ? (char*)obs_dev + real * (size_t)b0 * nobs2 : nullptr, 1.0 / n_snap, s);
+      c.launches += 3;
+    }
+  }
+  c.ops->finalize(c, n_snap, mean_tke_dev, nonfinite_dev, s);
+  c.launches += 1;
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int kf_step_host(kf_handle h, void* omega_hat_host, const void* actions_host, void* obs_host, void* mean_tke_host,
+                 int* nonfinite_host) {
+  if (!h || !omega_hat_host) return fail("kf_step_host: null argument");
+  Ctx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  const size_t el = c.ops->elem, real = el / 2;
+  const size_t B = c.cfg.B;
+  const size_t om_bytes = el * B * c.N * (c.MH + 1);
+  const size_t nobs2 = (size_t)c.cfg.obs_size * c.cfg.obs_size;
+  if (!c.d_omega) {
+    if (int rc = dev_alloc(c, &c.d_omega, om_bytes)) return rc;
+    if (int rc = dev_alloc(c, &c.d_act, real * B * 4)) return rc;
+    if (int rc = dev_alloc(c, &c.d_obs, real * B * nobs2)) return rc;
+    if (int rc = dev_alloc(c, &c.d_tke, real * B)) return rc;
+    if (int rc = dev_alloc(c, (void**)&c.d_nonf, sizeof(int) * B)) return rc;
+  }
+  cudaStream_t s = cudaStreamPerThread;
+  KF_CUDA(cudaMemcpyAsync(c.d_omega, omega_hat_host, om_bytes, cudaMemcpyHostToDevice, s));
+  if (actions_host) KF_CUDA(cudaMemcpyAsync(c.d_act, actions_host, real * B * 4, cudaMemcpyHostToDevice, s));
+  if (int rc = drive(c, c.d_omega, actions_host ? c.d_act : nullptr, nullptr, c.cfg.n_outer, c.cfg.n_inner, true,
+                     c.d_obs, c.d_tke, c.d_nonf, s))
+    return rc;
+  KF_CUDA(cudaMemcpyAsync(omega_hat_host, c.d_omega, om_bytes, cudaMemcpyDeviceToHost, s));
+  if (obs_host) KF_CUDA(cudaMemcpyAsync(obs_host, c.d_obs, real * B * nobs2, cudaMemcpyDeviceToHost, s));
+  if (mean_tke_host) KF_CUDA(cudaMemcpyAsync(mean_tke_host, c.d_tke, real * B, cudaMemcpyDeviceToHost, s));
+  if (nonfinite_host) KF_CUDA(cudaMemcpyAsync(nonfinite_host, c.d_nonf, sizeof(int) * B, cudaMemcpyDeviceToHost, s));
+  KF_CUDA(cudaStreamSynchronize(s));
+  return 0;
+}
+
+}  // extern "C"

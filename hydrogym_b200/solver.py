@@ -1,0 +1,166 @@
+"""Device-side stepper: owns a ``kf_handle`` and launches the sm_100a kernels on torch tensors.
+
+PyTorch is plumbing here (device memory, streams); all arithmetic of the hot path
+runs in ``libkolmo_b200.so``.  Mirrors what ``KolmogorovFlow._rollout``
+(hydrogym/jax/envs/kolmogorov.py:397-420) + ``RungeKuttaCrankNicolson.solve``
+(hydrogym/jax/solvers/base.py:82-116) do for a ``vmap``-ed batch.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib, constants
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+class KolmogorovStepper:
+    """Batched pseudo-spectral RK4-CN stepper for B environments on one GPU."""
+
+    def __init__(self, grid_size=(64, 64), Re=200, k=4, control_ks=(4, 5, 6, 7), dt=1e-3, n_inner=999,
+                 n_outer=10, num_envs=1, dtype=torch.float32, device=None, dealias=False, obs_size=8,
+                 min_action=-0.5, max_action=0.5, domain_x=(0, 2 * np.pi), domain_y=(0, 2 * np.pi),
+                 chunk=0, use_graph=True):
+        if dtype not in (torch.float32, torch.float64):
+            raise ValueError("dtype must be torch.float32 or torch.float64")
+        N, M = grid_size
+        if N != M:
+            raise ValueError("only square grids are supported")
+        if not torch.cuda.is_available():
+            raise RuntimeError("hydrogym_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        if self.device.type != "cuda":
+            raise RuntimeError("hydrogym_b200 runs on CUDA devices only")
+        dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", dev_index)
+        self.N, self.M, self.Mh = N, M, M // 2 + 1
+        self.B = int(num_envs)
+        self.dtype = dtype
+        self.cdtype = torch.complex64 if dtype == torch.float32 else torch.complex128
+        self.n_inner, self.n_outer = int(n_inner), int(n_outer)
+        self.obs_size = int(obs_size)
+        self.dt, self.nu = float(dt), 1.0 / Re
+
+        self._lib = _lib.load()
+        cfg = _lib.KfConfig(N=N, M=M, B=self.B, dtype=_lib.KF_F32 if dtype == torch.float32 else _lib.KF_F64,
+                            nu=self.nu, dt=self.dt, n_inner=self.n_inner, n_outer=self.n_outer,
+                            dealias=int(bool(dealias)), drag=0.0, device=dev_index, obs_size=self.obs_size,
+                            min_action=float(min_action), max_action=float(max_action), chunk=int(chunk),
+                            use_graph=int(bool(use_graph)))
+        self._h = ctypes.c_void_p(0)
+        _lib.check(self._lib.kf_create(ctypes.byref(self._h), ctypes.byref(cfg)), "kf_create")
+
+        np_c = np.complex64 if dtype == torch.float32 else np.complex128
+        self.forcing_row = np.ascontiguousarray(constants.forcing_row(k, grid_size, domain_y).astype(np_c))
+        self.control_rows = np.ascontiguousarray(constants.control_rows(control_ks, grid_size, domain_y).astype(np_c))
+        _lib.check(self._lib.kf_set_constants(self._h, self.forcing_row.ctypes.data_as(ctypes.c_void_p),
+                                              self.control_rows.ctypes.data_as(ctypes.c_void_p)), "kf_set_constants")
+
+    def set_control_rows(self, rows):
+        """Replace the 4 control basis rows (row kx=0 of control_term for unit actions)."""
+        np_c = np.complex64 if self.dtype == torch.float32 else np.complex128
+        self.control_rows = np.ascontiguousarray(np.asarray(rows).astype(np_c))
+        _lib.check(self._lib.kf_set_constants(self._h, self.forcing_row.ctypes.data_as(ctypes.c_void_p),
+                                              self.control_rows.ctypes.data_as(ctypes.c_void_p)), "kf_set_constants")
+
+    # -- helpers -------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.kf_destroy(self._h)
+            self._h = ctypes.c_void_p(0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _check_state(self, omega_hat):
+        if omega_hat.shape != (self.B, self.N, self.Mh) or omega_hat.dtype != self.cdtype:
+            raise ValueError(f"omega_hat must be {(self.B, self.N, self.Mh)} {self.cdtype}, "
+                             f"got {tuple(omega_hat.shape)} {omega_hat.dtype}")
+        if omega_hat.device != self.device or not omega_hat.is_contiguous():
+            raise ValueError("omega_hat must be a contiguous tensor on the stepper's device")
+
+    def _check_actions(self, actions):
+        if actions is None:
+            return None
+        actions = actions.to(device=self.device, dtype=self.dtype).contiguous()
+        if actions.shape != (self.B, 4):
+            raise ValueError(f"actions must be {(self.B, 4)}, got {tuple(actions.shape)}")
+        return actions
+
+    @property
+    def launch_count(self):
+        return int(self._lib.kf_launch_count(self._h))
+
+    @property
+    def workspace_bytes(self):
+        return int(self._lib.kf_workspace_bytes(self._h))
+
+    @property
+    def chunk(self):
+        return int(self._lib.kf_chunk(self._h))
+
+    # -- device entry points ---------------------------------------------------
+    def rk_steps(self, omega_hat, actions, n_steps):
+        """Advance ``omega_hat`` (B, N, Mh) IN PLACE by ``n_steps`` RK solver steps."""
+        self._check_state(omega_hat)
+        actions = self._check_actions(actions)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.kf_rk_steps(self._h, _ptr(omega_hat), _ptr(actions), int(n_steps), self._stream()),
+                       "kf_rk_steps")
+        return omega_hat
+
+    def rollout(self, omega_hat, actions=None, want_trajectory=True):
+        """``_rollout``: returns (final_state, trajectory[B, n_outer, N, Mh]); input is not modified."""
+        self._check_state(omega_hat)
+        actions = self._check_actions(actions)
+        final = omega_hat.clone()
+        traj = (torch.empty((self.B, self.n_outer, self.N, self.Mh), dtype=self.cdtype, device=self.device)
+                if want_trajectory else None)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.kf_rollout(self._h, _ptr(final), _ptr(actions), _ptr(traj), self._stream()),
+                       "kf_rollout")
+        return final, traj
+
+    def reward_obs(self, trajectory):
+        """(obs[B, obs_size^2], mean_tke[B], nonfinite[B]) of a trajectory (B, T, N, Mh)."""
+        if trajectory.dim() != 4 or trajectory.shape[0] != self.B or trajectory.shape[2:] != (self.N, self.Mh):
+            raise ValueError("trajectory must be (B, T, N, Mh)")
+        trajectory = trajectory.contiguous()
+        obs = torch.empty((self.B, self.obs_size ** 2), dtype=self.dtype, device=self.device)
+        tke = torch.empty((self.B,), dtype=self.dtype, device=self.device)
+        nonf = torch.empty((self.B,), dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.kf_reward_obs(self._h, _ptr(trajectory), int(trajectory.shape[1]), _ptr(obs),
+                                               _ptr(tke), _ptr(nonf), self._stream()), "kf_reward_obs")
+        return obs, tke, nonf
+
+    def step(self, omega_hat, actions=None, want_trajectory=True, in_place=False):
+        """Rollout + reward/obs in one call: (final, trajectory|None, obs, mean_tke, nonfinite)."""
+        self._check_state(omega_hat)
+        actions = self._check_actions(actions)
+        final = omega_hat if in_place else omega_hat.clone()
+        traj = (torch.empty((self.B, self.n_outer, self.N, self.Mh), dtype=self.cdtype, device=self.device)
+                if want_trajectory else None)
+        obs = torch.empty((self.B, self.obs_size ** 2), dtype=self.dtype, device=self.device)
+        tke = torch.empty((self.B,), dtype=self.dtype, device=self.device)
+        nonf = torch.empty((self.B,), dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.kf_step(self._h, _ptr(final), _ptr(actions), _ptr(traj), _ptr(obs), _ptr(tke),
+                                         _ptr(nonf), self._stream()), "kf_step")
+        return final, traj, obs, tke, nonf
+
+    def step_host(self, omega_hat_host, actions_host, obs_host, tke_host, nonf_host):
+        """``kf_step_host``: all arguments are HOST tensors (pinned for speed); synchronous, in place."""
+        _lib.check(self._lib.kf_step_host(self._h, _ptr(omega_hat_host), _ptr(actions_host), _ptr(obs_host),
+                                          _ptr(tke_host), _ptr(nonf_host)), "kf_step_host")

@@ -1,0 +1,95 @@
+/* kolmo_b200 -- C ABI of the B200-native Kolmogorov-flow environment step.
+ *
+ * Drop-in boundary for the hot path of hydrogym/jax (reference citations are
+ * relative to the reference repository root):
+ *   hydrogym/jax/envs/kolmogorov.py:397-420   KolmogorovFlow._rollout
+ *   hydrogym/jax/solvers/base.py:32-59,82-116 RungeKuttaCrankNicolson.RK4_CN / solve
+ *   hydrogym/jax/envs/kolmogorov.py:222-257   PseudoSpectralNavierStokes2D.nonlinear_terms
+ *   hydrogym/jax/envs/kolmogorov.py:426-470   _trajectory_mean_obs / _avg_tke / _reward
+ * The reference has no FFI for this path (it is pure JAX); these entry points are
+ * what a ctypes binding inside KolmogorovFlow would call.
+ *
+ * Conventions: every function returns 0 on success, non-zero on error (message via
+ * kf_last_error()); nothing throws across the ABI.  Complex numbers are interleaved
+ * (re, im) exactly like numpy / torch complex64 / complex128.  Pointers named *_dev
+ * are device pointers on the handle's device; `stream` is a cudaStream_t passed as
+ * void* (NULL = legacy default stream).  Calls are asynchronous on `stream` unless
+ * stated otherwise.  A handle is not thread-safe.
+ */
+#ifndef KOLMO_B200_H
+#define KOLMO_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct kf_handle_s* kf_handle;
+
+#define KF_F32 0
+#define KF_F64 1
+
+typedef struct kf_config {
+  int N, M;          /* grid_size (kolmogorov.py:35); square power of two, 64..1024 */
+  int B;             /* number of environments (VecEnv batch, env_core.py:609-613) */
+  int dtype;         /* KF_F32 / KF_F64 */
+  double nu;         /* 1/Re (kolmogorov.py:152-154) */
+  double dt;         /* RK step (kolmogorov.py:317, fixed at construction, base.py:54-55) */
+  int n_inner;       /* int(save_n // dt)        (base.py:100) */
+  int n_outer;       /* int(end // dt) // n_inner (base.py:102-103) */
+  int dealias;       /* 0 = reference behaviour (utils.py:72-86 is a no-op); 1 = intended 2/3 mask */
+  double drag;       /* must be 0.0: the reference has no drag term */
+  int device;        /* CUDA device ordinal */
+  int obs_size;      /* probes per side (kolmogorov.py:30) */
+  double min_action, max_action; /* clip range (kolmogorov.py:312-313, env_core.py:419-420) */
+  int chunk;         /* environments advanced together (L2 blocking); 0 = auto */
+  int use_graph;     /* 1 = replay RK steps from a CUDA graph */
+} kf_config;
+
+const char* kf_last_error(void);
+
+/* Allocates the workspace (h buffers, x-space fields, twiddles) on cfg->device. */
+int kf_create(kf_handle* out, const kf_config* cfg);
+int kf_destroy(kf_handle h);
+
+/* Host pointers, in the handle's dtype: forcing_row[M/2+1] complex is row kx=0 of
+ * forcing_term() (kolmogorov.py:274-292); control_rows[4][M/2+1] complex are row kx=0
+ * of control_term() for unit actions on k1..k4 (kolmogorov.py:259-272, 386-395).
+ * Synchronous. */
+int kf_set_constants(kf_handle h, const void* forcing_row, const void* control_rows);
+
+/* _rollout: advance omega_hat_dev [B][N][M/2+1] complex IN PLACE by n_outer*n_inner RK
+ * steps under actions_dev [B][4] real (NULL = no control, the reset path) and write the
+ * n_outer snapshots to trajectory_dev [B][n_outer][N][M/2+1] (NULL = skip). */
+int kf_rollout(kf_handle h, void* omega_hat_dev, const void* actions_dev, void* trajectory_dev, void* stream);
+
+/* Same solver at RK-step granularity (tests / benchmarks): n_steps RK steps, no snapshots. */
+int kf_rk_steps(kf_handle h, void* omega_hat_dev, const void* actions_dev, int n_steps, void* stream);
+
+/* _trajectory_mean_obs + _avg_tke of trajectory_dev [B][n_snap][N][M/2+1]:
+ * obs_dev [B][obs_size^2] real, mean_tke_dev [B] real, nonfinite_dev [B] int32 (each may be NULL). */
+int kf_reward_obs(kf_handle h, const void* trajectory_dev, int n_snap, void* obs_dev, void* mean_tke_dev,
+                  int* nonfinite_dev, void* stream);
+
+/* step_env's device work in one call: kf_rollout + kf_reward_obs, the reward/obs
+ * reductions running on the snapshots while they are still on chip-side buffers. */
+int kf_step(kf_handle h, void* omega_hat_dev, const void* actions_dev, void* trajectory_dev, void* obs_dev,
+            void* mean_tke_dev, int* nonfinite_dev, void* stream);
+
+/* kf_step with HOST buffers (pinned or pageable): copies omega_hat and actions in, runs
+ * the step, copies omega_hat, obs, mean_tke, nonfinite out; synchronous. */
+int kf_step_host(kf_handle h, void* omega_hat_host, const void* actions_host, void* obs_host,
+                 void* mean_tke_host, int* nonfinite_host);
+
+/* Number of kernels this handle has launched (or replayed from graphs) so far. */
+long long kf_launch_count(kf_handle h);
+/* Bytes of device memory owned by the handle. */
+size_t kf_workspace_bytes(kf_handle h);
+/* Environments per chunk actually used. */
+int kf_chunk(kf_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KOLMO_B200_H */

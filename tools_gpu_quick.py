@@ -1,0 +1,34 @@
+"""Scratch GPU timing of the flagship configuration (not the bench)."""
+import sys, time
+import numpy as np, torch
+from hydrogym_b200 import KolmogorovStepper
+
+def run(N, B, dtype, steps=20, **kw):
+    st = KolmogorovStepper(grid_size=(N, N), Re=1000, num_envs=B, dtype=dtype, device="cuda:0", **kw)
+    cd = torch.complex64 if dtype == torch.float32 else torch.complex128
+    g = torch.Generator(device="cuda").manual_seed(0)
+    w = torch.randn(B, N, N // 2 + 1, dtype=cd, device="cuda", generator=g)
+    p = torch.fft.fftfreq(N, 1.0 / N, device="cuda")[:, None]; q = torch.arange(N // 2 + 1, device="cuda")[None, :]
+    w = w * torch.exp(-(p * p + q * q) / 64.0) * N * N * 0.5
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        st.rk_steps(w, None, 8)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(s); st.rk_steps(w, None, steps); e1.record(s)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    w_bytes = 8 if dtype == torch.float32 else 16
+    C = N * (N // 2 + 1) * w_bytes
+    gbs = 70 * C * B / (ms * 1e-3) / 1e9
+    print(f"N={N} B={B} {dtype} {kw}: {ms:.3f} ms/RK-step  {B/ms*1e3:.0f} RKsteps*env/s  alg {gbs:.0f} GB/s ({gbs/6545*100:.1f}%) finite={bool(torch.isfinite(torch.view_as_real(w)).all())}", flush=True)
+    st.close()
+
+if __name__ == "__main__":
+    run(256, 256, torch.float32, steps=40)
+    run(256, 256, torch.float32, steps=40, use_graph=False)
+    for ch in (16, 32, 64, 128):
+        run(256, 256, torch.float32, steps=40, chunk=ch)
+    run(256, 256, torch.float64, steps=20)
+    run(128, 1024, torch.float32, steps=20)
+    run(1024, 16, torch.float32, steps=10)
+    run(64, 1, torch.float64, steps=200)
