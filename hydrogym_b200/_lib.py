@@ -16,7 +16,8 @@ KF_F32, KF_F64 = 0, 1
 # every symbol include/kolmo_b200.h declares
 SYMBOLS = (
     "kf_last_error", "kf_create", "kf_destroy", "kf_set_constants", "kf_rollout", "kf_rk_steps",
-    "kf_reward_obs", "kf_step", "kf_step_host", "kf_launch_count", "kf_workspace_bytes", "kf_chunk",
+    "kf_reward_obs", "kf_step", "kf_step_host", "kf_profile_kernels", "kf_launch_count", "kf_workspace_bytes",
+    "kf_chunk",
 )
 
 
@@ -55,8 +56,10 @@ def load():
     lib.kf_reward_obs.argtypes = [vp, vp, ctypes.c_int, vp, vp, vp, vp]
     lib.kf_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
     lib.kf_step_host.argtypes = [vp, vp, vp, vp, vp, vp]
+    fp = ctypes.POINTER(ctypes.c_float)
+    lib.kf_profile_kernels.argtypes = [vp, ctypes.c_int, fp, fp, vp]
     for name in ("kf_create", "kf_destroy", "kf_set_constants", "kf_rollout", "kf_rk_steps", "kf_reward_obs",
-                 "kf_step", "kf_step_host", "kf_chunk"):
+                 "kf_step", "kf_step_host", "kf_profile_kernels", "kf_chunk"):
         getattr(lib, name).restype = ctypes.c_int
     lib.kf_launch_count.argtypes = [vp]
     lib.kf_launch_count.restype = ctypes.c_longlong

@@ -33,7 +33,7 @@ template <typename T> struct StageArgs {
   const Cx<T>* tw;     // [N] exp(-2*pi*i*m/N)
   T beta, gdt, munu;   // beta_s, gamma_s*dt, mu_s*nu
   T scale;             // 1/(N*M), folded into the prologue
-  int do_epi, do_pro, dealias, nfld;
+  int dealias;
 };
 
 // exchange policy of the column kernel: TC columns interleaved, conflict-free
@@ -55,23 +55,91 @@ template <typename T, int TPF> struct RowEx {
   }
 };
 
-template <int N> __device__ __forceinline__ int wavenum(int i) { return i < N / 2 ? i : i - N; }
-
-// real coefficient c such that field_hat = c * (i * omega_hat); f: 0 u, 1 v, 2 gx, 3 gy
-template <typename T> __device__ __forceinline__ T field_coef(int f, T p, T q, T scale) {
-  const T k2 = p * p + q * q;
-  const T ik2 = k2 > (T)0 ? scale / k2 : (T)0;
-  return f == 0 ? q * ik2 : f == 1 ? -p * ik2 : f == 2 ? p * scale : q * scale;
+// 1/x: MUFU.RCP + one Newton step for fp32 (branch-free, ~1 ulp); IEEE division for fp64
+__device__ __forceinline__ float fast_rcp(float x) {
+  float r = __fdividef(1.0f, x);
+  return fmaf(r, fmaf(-x, r, 1.0f), r);
 }
+__device__ __forceinline__ double fast_rcp(double x) { return 1.0 / x; }
+
+// integer wavenumber p of row kx = t + TPF*m as a real: the wrap at N/2 depends on m only
+template <typename T, class P> __device__ __forceinline__ T wave_p(T tf, int m) {
+  return tf + (T)(P::TPF * m - (m >= P::E / 2 ? P::L : 0));
+}
+
+// coefficient c with field_hat = c * (i * omega_hat) given sp = p*scale, sq = q*scale, ik2 = 1/(p^2+q^2)
+// (0 at p=q=0).  F: 0 u_hat = i q w / k^2, 1 v_hat = -i p w / k^2, 2 gx_hat = i p w, 3 gy_hat = i q w
+// (kolmogorov.py:236-246 with 2*pi*kx = p, 2*pi*ky = q).
+template <int F, typename T> __device__ __forceinline__ T field_coef(T sp, T sq, T ik2) {
+  return F == 0 ? sq * ik2 : F == 1 ? -(sp * ik2) : F == 2 ? sp : sq;
+}
+template <typename T> __device__ __forceinline__ T inv_k2(T p, T q) {
+  const T k2 = p * p + q * q;
+  return k2 > (T)0 ? fast_rcp(k2) : (T)0;
+}
+
+enum ColMode { kColStage = 0, kColInit = 1, kColObs = 2 };
 
 // ---------------------------------------------------------------------------
 // Column kernel.  grid = (M/2 / TC, Bc), block = TPF*TC threads; thread (c, t)
 // owns column q = tile*TC + c and rows {t + TPF*m}: every global access is a run
 // of TC consecutive complex numbers per row (128 B for TC=16 complex64).
 // Tile 0 also carries the ky = M/2 column, packed with ky = 0 in x-space.
+//   MODE kColStage : epilogue of a sub-stage + prologue (4 fields) for the next one
+//   MODE kColInit  : prologue only (4 fields) from the stored omega_hat
+//   MODE kColObs   : prologue only, u_hat and v_hat (reward / observation path)
 // ---------------------------------------------------------------------------
-template <typename T, class P, int TC>
-__global__ void __launch_bounds__(P::TPF* TC) col_kernel(StageArgs<T> a) {
+#ifndef KF_MINB_COL
+#define KF_MINB_COL 2
+#endif
+
+template <int F, typename T, class P, int TC>
+__device__ __forceinline__ void col_field(const StageArgs<T>& a, const Cx<T>* w, const Cx<T>* s_tw, Cx<T>* s_nyq,
+                                          Cx<T>* s_ex, ColEx<T, TC>& ex, int c, int t, int q, int b, bool special) {
+  constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
+  const T tf = (T)t, sq = (T)q * a.scale;
+  Cx<T> v[E];
+#pragma unroll
+  for (int m = 0; m < E; ++m) {
+    const T p = wave_p<T, P>(tf, m);
+    const T cf = field_coef<F, T>(p * a.scale, sq, (F < 2) ? inv_k2<T>(p, (T)q) : (T)0);
+    v[m] = cf * mul_i(w[m]);
+  }
+  if (special) {
+    // column 0 <- herm(field[:,0]) + i*herm(field[:,M/2]); herm(a)[kx] = (a[kx]+conj(a[-kx]))/2
+    Cx<T>* sA = s_ex;
+    Cx<T>* sB = s_ex + N;
+    if (c == 0) {
+#pragma unroll
+      for (int m = 0; m < E; ++m) {
+        const int kx = t + TPF * m;
+        const T p = wave_p<T, P>(tf, m);
+        const T cf = field_coef<F, T>(p * a.scale, (T)MH * a.scale, (F < 2) ? inv_k2<T>(p, (T)MH) : (T)0);
+        stc(sA + kx, v[m]);
+        stc(sB + kx, cf * mul_i(ldc(s_nyq + kx)));
+      }
+    }
+    __syncthreads();
+    if (c == 0) {
+#pragma unroll
+      for (int m = 0; m < E; ++m) {
+        const int kx = t + TPF * m;
+        const int mkx = (N - kx) & (N - 1);
+        const Cx<T> ah = (T)0.5 * (v[m] + conj(ldc(sA + mkx)));
+        const Cx<T> bh = (T)0.5 * (ldc(sB + kx) + conj(ldc(sB + mkx)));
+        v[m] = mk<T>(ah.x - bh.y, ah.y + bh.x);
+      }
+    }
+    __syncthreads();
+  }
+  fft_regs<P, +1, T>(v, s_tw, t, ex);
+  Cx<T>* out = a.fld + F * a.fstride + (size_t)b * N * MH + q;
+#pragma unroll
+  for (int m = 0; m < E; ++m) stc(out + (size_t)(t + TPF * m) * MH, v[m]);
+}
+
+template <typename T, class P, int TC, int MODE>
+__global__ void __launch_bounds__(P::TPF* TC, KF_MINB_COL) col_kernel(StageArgs<T> a) {
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw);
@@ -81,9 +149,9 @@ __global__ void __launch_bounds__(P::TPF* TC) col_kernel(StageArgs<T> a) {
   const int b = blockIdx.y;
   const int q = blockIdx.x * TC + c;
   const bool special = (blockIdx.x == 0);  // CTA-uniform
-  const T qf = (T)q;
+  const T qf = (T)q, tf = (T)t;
   const size_t plane = (size_t)N * MH;
-  Cx<T>* wmain = a.wmain + b * plane;
+  Cx<T>* wmain = a.wmain + b * plane + q;
   Cx<T>* wnyq = a.wnyq + (size_t)b * N;
 
   for (int i = threadIdx.x; i < N; i += TPF * TC) s_tw[i] = ldc(a.tw + i);
@@ -92,15 +160,15 @@ __global__ void __launch_bounds__(P::TPF* TC) col_kernel(StageArgs<T> a) {
   ColEx<T, TC> ex{s_ex, c};
   Cx<T> w[E];
 
-  if (a.do_epi) {
-    Cx<T>* hmain = a.hmain + b * plane;
+  if constexpr (MODE == kColStage) {
+    Cx<T>* hmain = a.hmain + b * plane + q;
     Cx<T>* hnyq = a.hnyq + (size_t)b * N;
     const Cx<T>* G = a.G + (size_t)b * (MH + 1);
-    const Cx<T>* advx = a.advx + b * plane;
+    const Cx<T>* advx = a.advx + b * plane + q;
     const bool use_h = (a.beta != (T)0);
     Cx<T> v[E];
 #pragma unroll
-    for (int m = 0; m < E; ++m) v[m] = ldc(advx + (size_t)(t + TPF * m) * MH + q);
+    for (int m = 0; m < E; ++m) v[m] = ldc(advx + (size_t)(t + TPF * m) * MH);
     fft_regs<P, -1, T>(v, s_tw, t, ex);
 
     if (special) {
@@ -123,10 +191,10 @@ __global__ void __launch_bounds__(P::TPF* TC) col_kernel(StageArgs<T> a) {
           Cx<T> h = nl;
           if (use_h) h = h + a.beta * ldc(hnyq + kx);
           stc(hnyq + kx, h);
-          const T p = (T)wavenum<N>(kx);
+          const T p = wave_p<T, P>(tf, m);
           const T lk = a.munu * (p * p + (T)MH * (T)MH);
           Cx<T> wv = ldc(wnyq + kx);
-          wv = ((T)1 / ((T)1 + lk)) * (wv + a.gdt * h - lk * wv);
+          wv = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
           stc(wnyq + kx, wv);
           stc(s_nyq + kx, wv);
         }
@@ -134,72 +202,36 @@ __global__ void __launch_bounds__(P::TPF* TC) col_kernel(StageArgs<T> a) {
       __syncthreads();
     }
 
-    const int kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3;
+    constexpr int kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3;
 #pragma unroll
     for (int m = 0; m < E; ++m) {
       const int kx = t + TPF * m;
-      const size_t off = (size_t)kx * MH + q;
-      Cx<T> nl = v[m];
-      if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) nl = mk<T>((T)0, (T)0);
-      if (kx == 0) nl = nl + ldc(G + q);
-      Cx<T> h = nl;
+      const size_t off = (size_t)kx * MH;
+      Cx<T> h = v[m];
+      if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) h = mk<T>((T)0, (T)0);
+      if (m == 0 && t == 0) h = h + ldc(G + q);
       if (use_h) h = h + a.beta * ldc(hmain + off);
       stc(hmain + off, h);
-      const T p = (T)wavenum<N>(kx);
+      const T p = wave_p<T, P>(tf, m);
       const T lk = a.munu * (p * p + qf * qf);
       const Cx<T> wv = ldc(wmain + off);
-      w[m] = ((T)1 / ((T)1 + lk)) * (wv + a.gdt * h - lk * wv);
+      w[m] = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
       stc(wmain + off, w[m]);
     }
   } else {
 #pragma unroll
-    for (int m = 0; m < E; ++m) w[m] = ldc(wmain + (size_t)(t + TPF * m) * MH + q);
+    for (int m = 0; m < E; ++m) w[m] = ldc(wmain + (size_t)(t + TPF * m) * MH);
     if (special) {
       for (int i = threadIdx.x; i < N; i += TPF * TC) s_nyq[i] = ldc(wnyq + i);
       __syncthreads();
     }
   }
 
-  if (a.do_pro) {
-#pragma unroll 1
-    for (int f = 0; f < a.nfld; ++f) {
-      Cx<T> v[E];
-#pragma unroll
-      for (int m = 0; m < E; ++m) {
-        const T p = (T)wavenum<N>(t + TPF * m);
-        v[m] = field_coef<T>(f, p, qf, a.scale) * mul_i(w[m]);
-      }
-      if (special) {
-        // column 0 <- herm(field[:,0]) + i*herm(field[:,M/2]); herm(a)[kx] = (a[kx]+conj(a[-kx]))/2
-        Cx<T>* sA = s_ex;
-        Cx<T>* sB = s_ex + N;
-        if (c == 0) {
-#pragma unroll
-          for (int m = 0; m < E; ++m) {
-            const int kx = t + TPF * m;
-            const T p = (T)wavenum<N>(kx);
-            stc(sA + kx, v[m]);
-            stc(sB + kx, field_coef<T>(f, p, (T)MH, a.scale) * mul_i(ldc(s_nyq + kx)));
-          }
-        }
-        __syncthreads();
-        if (c == 0) {
-#pragma unroll
-          for (int m = 0; m < E; ++m) {
-            const int kx = t + TPF * m;
-            const int mkx = (N - kx) & (N - 1);
-            const Cx<T> ah = (T)0.5 * (v[m] + conj(ldc(sA + mkx)));
-            const Cx<T> bh = (T)0.5 * (ldc(sB + kx) + conj(ldc(sB + mkx)));
-            v[m] = mk<T>(ah.x - bh.y, ah.y + bh.x);
-          }
-        }
-        __syncthreads();
-      }
-      fft_regs<P, +1, T>(v, s_tw, t, ex);
-      Cx<T>* out = a.fld + f * a.fstride + b * plane;
-#pragma unroll
-      for (int m = 0; m < E; ++m) stc(out + (size_t)(t + TPF * m) * MH + q, v[m]);
-    }
+  col_field<0, T, P, TC>(a, w, s_tw, s_nyq, s_ex, ex, c, t, q, b, special);
+  col_field<1, T, P, TC>(a, w, s_tw, s_nyq, s_ex, ex, c, t, q, b, special);
+  if constexpr (MODE != kColObs) {
+    col_field<2, T, P, TC>(a, w, s_tw, s_nyq, s_ex, ex, c, t, q, b, special);
+    col_field<3, T, P, TC>(a, w, s_tw, s_nyq, s_ex, ex, c, t, q, b, special);
   }
 }
 
@@ -232,7 +264,10 @@ __device__ __forceinline__ void load_pair_hermitian(Cx<T>* z, const Cx<T>* __res
 }
 
 template <typename T, class P, int GROUPS>
-__global__ void __launch_bounds__(P::TPF* GROUPS) row_kernel(StageArgs<T> a) {
+#ifndef KF_MINB_ROW
+#define KF_MINB_ROW 1
+#endif
+__global__ void __launch_bounds__(P::TPF* GROUPS, KF_MINB_ROW) row_kernel(StageArgs<T> a) {
   constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF, N = M;
   constexpr int EXN = M + M / 16;
   extern __shared__ __align__(16) unsigned char smem_raw[];

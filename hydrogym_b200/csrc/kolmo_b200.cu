@@ -44,7 +44,7 @@ struct Ops {
   size_t col_smem, row_smem;
   cudaError_t (*prepare)();
   // all of these work on the chunk-local workspace; nb = environments in the chunk
-  void (*col)(const struct Ctx&, int nb, const Stage&, int do_epi, int do_pro, int nfld, cudaStream_t);
+  void (*col)(const struct Ctx&, int nb, const Stage&, int mode, cudaStream_t);
   void (*row)(const struct Ctx&, int nb, cudaStream_t);
   // obs_dev / acc already offset to the chunk's first environment
   void (*obs)(const struct Ctx&, int nb, double* acc, size_t acc_stride, void* obs_dev, double obs_w, cudaStream_t);
@@ -85,7 +85,14 @@ template <typename T, class P, int TC, int GROUPS> struct Impl {
 
   static cudaError_t prepare() {
     cudaError_t e;
-    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem());
+    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColStage>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)col_smem());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColInit>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)col_smem());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColObs>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)col_smem());
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kf::row_kernel<T, P, GROUPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem());
     if (e != cudaSuccess) return e;
@@ -101,15 +108,17 @@ template <typename T, class P, int TC, int GROUPS> struct Impl {
     a.tw = (const C*)c.tw;
     a.beta = 0; a.gdt = 0; a.munu = 0;
     a.scale = (T)(1.0 / ((double)N * (double)N));
-    a.do_epi = 0; a.do_pro = 0; a.dealias = c.cfg.dealias; a.nfld = 4;
+    a.dealias = c.cfg.dealias;
     return a;
   }
 
-  static void col(const Ctx& c, int nb, const Stage& st, int do_epi, int do_pro, int nfld, cudaStream_t s) {
+  static void col(const Ctx& c, int nb, const Stage& st, int mode, cudaStream_t s) {
     kf::StageArgs<T> a = args(c);
     a.beta = (T)st.beta; a.gdt = (T)st.gdt; a.munu = (T)st.munu;
-    a.do_epi = do_epi; a.do_pro = do_pro; a.nfld = nfld;
-    kf::col_kernel<T, P, TC><<<dim3(MH / TC, nb), P::TPF * TC, col_smem(), s>>>(a);
+    const dim3 grid(MH / TC, nb);
+    if (mode == kf::kColStage) kf::col_kernel<T, P, TC, kf::kColStage><<<grid, P::TPF * TC, col_smem(), s>>>(a);
+    else if (mode == kf::kColInit) kf::col_kernel<T, P, TC, kf::kColInit><<<grid, P::TPF * TC, col_smem(), s>>>(a);
+    else kf::col_kernel<T, P, TC, kf::kColObs><<<grid, P::TPF * TC, col_smem(), s>>>(a);
   }
   static void row(const Ctx& c, int nb, cudaStream_t s) {
     kf::StageArgs<T> a = args(c);
@@ -189,7 +198,7 @@ Stage stage_of(const Ctx& c, int s) {
 void enqueue_rk_step(Ctx& c, int nb, cudaStream_t s) {
   for (int k = 0; k < 5; ++k) {
     c.ops->row(c, nb, s);
-    c.ops->col(c, nb, stage_of(c, k), 1, 1, 4, s);
+    c.ops->col(c, nb, stage_of(c, k), kf::kColStage, s);
   }
 }
 
@@ -262,7 +271,7 @@ int drive(Ctx& c, void* omega, const void* actions, void* traj, int n_outer, int
     char* om = (char*)omega + el * user_env * b0;
     c.ops->import_(c, nb, om, user_env, s);
     c.ops->forcing(c, nb, actions ? (const char*)actions + real * 4 * b0 : nullptr, s);
-    c.ops->col(c, nb, stage_of(c, 0), 0, 1, 4, s);  // fields of the initial state
+    c.ops->col(c, nb, stage_of(c, 0), kf::kColInit, s);  // fields of the initial state
     c.launches += 3;
     for (int j = 0; j < n_outer; ++j) {
       if (int rc = run_rk_steps(c, nb, n_inner, s)) return rc;
@@ -471,7 +480,7 @@ int kf_reward_obs(kf_handle h, const void* trajectory_dev, int n_snap, void* obs
     for (int j = 0; j < n_snap; ++j) {
       const char* tj = (const char*)trajectory_dev + el * user_env * ((size_t)b0 * n_snap + j);
       c.ops->import_(c, nb, tj, user_env * n_snap, s);
-      c.ops->col(c, nb, stage_of(c, 0), 0, 1, 2, s);  // u_hat, v_hat -> x-space
+      c.ops->col(c, nb, stage_of(c, 0), kf::kColObs, s);  // u_hat, v_hat -> x-space
       c.ops->obs(c, nb, c.acc + 4 * ((size_t)b0 * n_snap + j), 4 * (size_t)n_snap,
                  obs_dev ? (char*)obs_dev + real * (size_t)b0 * nobs2 : nullptr, 1.0 / n_snap, s);
       c.launches += 3;
@@ -510,6 +519,48 @@ int kf_step_host(kf_handle h, void* omega_hat_host, const void* actions_host, vo
   if (mean_tke_host) KF_CUDA(cudaMemcpyAsync(mean_tke_host, c.d_tke, real * B, cudaMemcpyDeviceToHost, s));
   if (nonfinite_host) KF_CUDA(cudaMemcpyAsync(nonfinite_host, c.d_nonf, sizeof(int) * B, cudaMemcpyDeviceToHost, s));
   KF_CUDA(cudaStreamSynchronize(s));
+  return 0;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+// Measurement aid for bench.py: time `reps` back-to-back launches of the column kernel
+// (sub-stage `stage`, epilogue + prologue) and of the row kernel on the current chunk
+// workspace with CUDA events on `stream`.  The workspace contents are advanced as in a
+// real run (each launch is a genuine sub-stage), so call it on scratch state only.
+int kf_profile_kernels(kf_handle h, int reps, float* ms_col, float* ms_row, void* stream) {
+  if (!h || reps < 1) return fail("kf_profile_kernels: bad argument");
+  Ctx& c = h->c;
+  if (!c.have_constants) return fail("kf_set_constants has not been called");
+  DeviceGuard guard(c.cfg.device);
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaEvent_t e0, e1, e2;
+  KF_CUDA(cudaEventCreate(&e0));
+  KF_CUDA(cudaEventCreate(&e1));
+  KF_CUDA(cudaEventCreate(&e2));
+  const int nb = c.chunk;
+  c.ops->forcing(c, nb, nullptr, s);
+  for (int i = 0; i < 3; ++i) {  // warm-up
+    c.ops->row(c, nb, s);
+    c.ops->col(c, nb, stage_of(c, 1), kf::kColStage, s);
+  }
+  KF_CUDA(cudaEventRecord(e0, s));
+  for (int i = 0; i < reps; ++i) c.ops->col(c, nb, stage_of(c, 1 + i % 4), kf::kColStage, s);
+  KF_CUDA(cudaEventRecord(e1, s));
+  for (int i = 0; i < reps; ++i) c.ops->row(c, nb, s);
+  KF_CUDA(cudaEventRecord(e2, s));
+  KF_CUDA(cudaEventSynchronize(e2));
+  float a = 0, b = 0;
+  KF_CUDA(cudaEventElapsedTime(&a, e0, e1));
+  KF_CUDA(cudaEventElapsedTime(&b, e1, e2));
+  if (ms_col) *ms_col = a / reps;
+  if (ms_row) *ms_row = b / reps;
+  c.launches += 2LL * reps + 7;
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaEventDestroy(e2);
   return 0;
 }
 

@@ -160,6 +160,14 @@ class KolmogorovStepper:
                                          _ptr(nonf), self._stream()), "kf_step")
         return final, traj, obs, tke, nonf
 
+    def profile_kernels(self, reps=20):
+        """(ms per column-kernel launch, ms per row-kernel launch) on scratch workspace data."""
+        a, b = ctypes.c_float(0), ctypes.c_float(0)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.kf_profile_kernels(self._h, int(reps), ctypes.byref(a), ctypes.byref(b),
+                                                    self._stream()), "kf_profile_kernels")
+        return float(a.value), float(b.value)
+
     def step_host(self, omega_hat_host, actions_host, obs_host, tke_host, nonf_host):
         """``kf_step_host``: all arguments are HOST tensors (pinned for speed); synchronous, in place."""
         _lib.check(self._lib.kf_step_host(self._h, _ptr(omega_hat_host), _ptr(actions_host), _ptr(obs_host),

@@ -82,6 +82,11 @@ int kf_step(kf_handle h, void* omega_hat_dev, const void* actions_dev, void* tra
 int kf_step_host(kf_handle h, void* omega_hat_host, const void* actions_host, void* obs_host,
                  void* mean_tke_host, int* nonfinite_host);
 
+/* Measurement aid: average duration (ms, CUDA events on `stream`) of `reps` back-to-back
+ * launches of the column kernel and of the row kernel on the chunk workspace.  Scratches
+ * the workspace; synchronous. */
+int kf_profile_kernels(kf_handle h, int reps, float* ms_col, float* ms_row, void* stream);
+
 /* Number of kernels this handle has launched (or replayed from graphs) so far. */
 long long kf_launch_count(kf_handle h);
 /* Bytes of device memory owned by the handle. */

@@ -1,5 +1,6 @@
 """Scratch GPU timing of the flagship configuration (not the bench)."""
-import sys, time
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from hydrogym_b200 import KolmogorovStepper
 
