@@ -9,7 +9,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libkolmo_b200.so")
+LIB_PATH = os.environ.get("KF_LIB") or os.path.join(_HERE, "libkolmo_b200.so")  # KF_LIB: experiments only
 
 KF_F32, KF_F64 = 0, 1
 

@@ -89,10 +89,6 @@ enum ColMode { kColStage = 0, kColInit = 1, kColObs = 2 };
 //   MODE kColInit  : prologue only (4 fields) from the stored omega_hat
 //   MODE kColObs   : prologue only, u_hat and v_hat (reward / observation path)
 // ---------------------------------------------------------------------------
-#ifndef KF_MINB_COL
-#define KF_MINB_COL 2
-#endif
-
 template <int F, typename T, class P, int TC>
 __device__ __forceinline__ void col_field(const StageArgs<T>& a, const Cx<T>* w, const Cx<T>* s_tw, Cx<T>* s_nyq,
                                           Cx<T>* s_ex, ColEx<T, TC>& ex, int c, int t, int q, int b, bool special) {
@@ -138,8 +134,8 @@ __device__ __forceinline__ void col_field(const StageArgs<T>& a, const Cx<T>* w,
   for (int m = 0; m < E; ++m) stc(out + (size_t)(t + TPF * m) * MH, v[m]);
 }
 
-template <typename T, class P, int TC, int MODE>
-__global__ void __launch_bounds__(P::TPF* TC, KF_MINB_COL) col_kernel(StageArgs<T> a) {
+template <typename T, class P, int TC, int MODE, int MINB>
+__global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw);
@@ -263,11 +259,8 @@ __device__ __forceinline__ void load_pair_hermitian(Cx<T>* z, const Cx<T>* __res
   }
 }
 
-template <typename T, class P, int GROUPS>
-#ifndef KF_MINB_ROW
-#define KF_MINB_ROW 1
-#endif
-__global__ void __launch_bounds__(P::TPF* GROUPS, KF_MINB_ROW) row_kernel(StageArgs<T> a) {
+template <typename T, class P, int GROUPS, int MINB>
+__global__ void __launch_bounds__(P::TPF* GROUPS, MINB) row_kernel(StageArgs<T> a) {
   constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF, N = M;
   constexpr int EXN = M + M / 16;
   extern __shared__ __align__(16) unsigned char smem_raw[];

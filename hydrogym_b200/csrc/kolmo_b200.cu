@@ -77,7 +77,9 @@ struct Ctx {
 };
 
 
-template <typename T, class P, int TC, int GROUPS> struct Impl {
+// TC: columns per column-kernel CTA; GROUPS: FFT groups per row-kernel CTA;
+// CB / RB: __launch_bounds__ min-blocks (register caps) of the column / row kernels.
+template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1> struct Impl {
   using C = kf::Cx<T>;
   static constexpr int N = P::L, MH = N / 2;
   static size_t col_smem() { return sizeof(C) * (2 * (size_t)N + (size_t)N * TC); }
@@ -85,16 +87,16 @@ template <typename T, class P, int TC, int GROUPS> struct Impl {
 
   static cudaError_t prepare() {
     cudaError_t e;
-    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColStage>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColStage, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)col_smem());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColInit>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColInit, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)col_smem());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColObs>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColObs, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)col_smem());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(kf::row_kernel<T, P, GROUPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem());
+    e = cudaFuncSetAttribute(kf::row_kernel<T, P, GROUPS, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem());
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(kf::row_obs_kernel<T, P, GROUPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)row_smem());
@@ -116,13 +118,13 @@ template <typename T, class P, int TC, int GROUPS> struct Impl {
     kf::StageArgs<T> a = args(c);
     a.beta = (T)st.beta; a.gdt = (T)st.gdt; a.munu = (T)st.munu;
     const dim3 grid(MH / TC, nb);
-    if (mode == kf::kColStage) kf::col_kernel<T, P, TC, kf::kColStage><<<grid, P::TPF * TC, col_smem(), s>>>(a);
-    else if (mode == kf::kColInit) kf::col_kernel<T, P, TC, kf::kColInit><<<grid, P::TPF * TC, col_smem(), s>>>(a);
-    else kf::col_kernel<T, P, TC, kf::kColObs><<<grid, P::TPF * TC, col_smem(), s>>>(a);
+    if (mode == kf::kColStage) kf::col_kernel<T, P, TC, kf::kColStage, CB><<<grid, P::TPF * TC, col_smem(), s>>>(a);
+    else if (mode == kf::kColInit) kf::col_kernel<T, P, TC, kf::kColInit, CB><<<grid, P::TPF * TC, col_smem(), s>>>(a);
+    else kf::col_kernel<T, P, TC, kf::kColObs, CB><<<grid, P::TPF * TC, col_smem(), s>>>(a);
   }
   static void row(const Ctx& c, int nb, cudaStream_t s) {
     kf::StageArgs<T> a = args(c);
-    kf::row_kernel<T, P, GROUPS><<<dim3(N / 2 / GROUPS, nb), P::TPF * GROUPS, row_smem(), s>>>(a);
+    kf::row_kernel<T, P, GROUPS, RB><<<dim3(N / 2 / GROUPS, nb), P::TPF * GROUPS, row_smem(), s>>>(a);
   }
   static void obs(const Ctx& c, int nb, double* acc, size_t acc_stride, void* obs_dev, double obs_w, cudaStream_t s) {
     kf::ObsArgs<T> a;
@@ -162,12 +164,12 @@ const Ops* find_ops(int dtype, int N) {
   using kf::Plan;
   static const Ops f64_[] = {Impl<float, Plan<64, 8, 8, 8>, 16, 16>::make()};
   static const Ops f128[] = {Impl<float, Plan<128, 8, 16, 8>, 16, 16>::make()};
-  static const Ops f256[] = {Impl<float, Plan<256, 16, 16, 16>, 16, 8>::make()};
+  static const Ops f256[] = {Impl<float, Plan<256, 16, 16, 16>, 16, 8, 3, 4>::make()};
   static const Ops f512[] = {Impl<float, Plan<512, 32, 8, 8, 8>, 8, 4>::make()};
   static const Ops f1024[] = {Impl<float, Plan<1024, 64, 16, 4, 16>, 8, 2>::make()};
   static const Ops d64[] = {Impl<double, Plan<64, 8, 8, 8>, 16, 16>::make()};
   static const Ops d128[] = {Impl<double, Plan<128, 16, 8, 2, 8>, 8, 8>::make()};
-  static const Ops d256[] = {Impl<double, Plan<256, 32, 8, 4, 8>, 8, 4>::make()};
+  static const Ops d256[] = {Impl<double, Plan<256, 32, 8, 4, 8>, 8, 4, 3, 4>::make()};
   static const Ops d512[] = {Impl<double, Plan<512, 64, 8, 8, 8>, 4, 2>::make()};
   static const Ops d1024[] = {Impl<double, Plan<1024, 128, 8, 2, 8, 8>, 4, 1>::make()};
   const bool f = dtype == KF_F32;
