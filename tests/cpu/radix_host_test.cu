@@ -15,7 +15,6 @@ template <int R, int DIR, typename T> double check() {
   }
   kf::Radix<R>::template run<DIR, T>(a);
   double err = 0;
-  const double kPi = 3.14159265358979323846;
   for (int k = 0; k < R; ++k) {
     long double re = 0, im = 0;
     for (int n = 0; n < R; ++n) {
@@ -34,7 +33,7 @@ int main() {
 #define RUN(R)                                                                              \
   e64 = std::fmax(e64, std::fmax(check<R, -1, double>(), check<R, +1, double>()));         \
   e32 = std::fmax(e32, std::fmax(check<R, -1, float>(), check<R, +1, float>()));
-  RUN(2) std::printf("%g ", e64); RUN(4) std::printf("%g ", e64); RUN(8) std::printf("%g ", e64); RUN(16) std::printf("%g ", e64); RUN(32)
+  RUN(2) RUN(4) RUN(8) RUN(16) RUN(32)
   std::printf("max_err_f64 %.3e max_err_f32 %.3e\n", e64, e32);
   return (e64 < 1e-13 && e32 < 1e-5) ? 0 : 1;
 }
