@@ -1,0 +1,187 @@
+// Persistent, TMA-fed column kernel for the RK sub-stage (sm_100a).
+//
+// Same arithmetic as col_kernel<..., kColStage> (kernels.cuh) but the three input tiles of a
+// (environment, 16-column) tile -- advection rows, RK register h, omega_hat -- arrive in shared
+// memory through cp.async.bulk.tensor (TMA, SASS UTMALDG) one tile AHEAD of their use, so the
+// FFT/pointwise phases never wait on a global load:
+//
+//   buffer   filled by TMA with     consumed by                      then reused as
+//   buf_adv  adv rows of tile i     first FFT pass (registers)       exchange buffer of the forward FFT
+//   buf_h    h of tile i            RK accumulate                    exchange buffer of the 4 inverse FFTs
+//   buf_w    omega_hat of tile i    Crank-Nicolson update            --
+//
+// As soon as a buffer's last reader has passed a barrier, thread 0 re-arms its mbarrier and
+// issues the load of the NEXT tile of this CTA (tile + gridDim.x): adv right after the forward
+// FFT, omega_hat after the update, h after the last inverse FFT.  Outputs leave with plain
+// coalesced stores.  One CTA = TPF*TC threads; grid = (#SMs x resident CTAs), tiles round-robin.
+#pragma once
+#include <cuda.h>  // CUtensorMap (type only; the encoder is fetched at run time)
+
+#include "kernels.cuh"
+
+namespace kf {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// 2-D tiled TMA load: box at element coordinates (c0 = inner, c1 = row) -> dense [rows][inner] in smem
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+          smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+
+template <typename T, class P, int TC> struct ColTmaSmem {
+  static constexpr int N = P::L;
+  static constexpr size_t kTile = (size_t)N * TC * sizeof(Cx<T>);
+  static constexpr size_t bytes() { return 3 * kTile + 2 * (size_t)N * sizeof(Cx<T>) + 64; }
+};
+
+template <typename T, class P, int TC, int MINB>
+__global__ void __launch_bounds__(P::TPF* TC, MINB)
+    col_tma_kernel(StageArgs<T> a, const __grid_constant__ CUtensorMap m_adv, const __grid_constant__ CUtensorMap m_h,
+                   const __grid_constant__ CUtensorMap m_w, int ntiles) {
+  constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2, TILES = MH / TC;
+  constexpr int RB = N < 256 ? N : 256, NBOX = N / RB;  // TMA box rows (<= 256)
+  constexpr uint32_t kBytes = (uint32_t)((size_t)N * TC * sizeof(Cx<T>));
+  extern __shared__ __align__(1024) unsigned char smem_tma[];
+  Cx<T>* buf_adv = reinterpret_cast<Cx<T>*>(smem_tma);
+  Cx<T>* buf_h = buf_adv + (size_t)N * TC;
+  Cx<T>* buf_w = buf_h + (size_t)N * TC;
+  Cx<T>* s_tw = buf_w + (size_t)N * TC;
+  Cx<T>* s_nyq = s_tw + N;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_nyq + N);  // [0] adv, [1] h, [2] w
+  const int tid = threadIdx.x, c = tid % TC, t = tid / TC;
+  const T tf = (T)t;
+  const bool use_h = (a.beta != (T)0);
+  const size_t plane = (size_t)N * MH;
+
+  if (tid == 0) {
+    mbar_init(bars + 0, 1);
+    mbar_init(bars + 1, 1);
+    mbar_init(bars + 2, 1);
+    fence_mbar_init();
+  }
+  for (int i = tid; i < N; i += TPF * TC) s_tw[i] = ldc(a.tw + i);
+  __syncthreads();
+
+  auto issue = [&](Cx<T>* buf, const CUtensorMap* map, uint64_t* bar, int tile) {
+    const int b = tile / TILES, tx = tile - b * TILES;
+    mbar_expect_tx(bar, kBytes);
+#pragma unroll
+    for (int r = 0; r < NBOX; ++r)
+      tma_load_2d(buf + (size_t)r * RB * TC, map, tx * TC * 2, b * N + r * RB, bar);
+  };
+
+  const int first = blockIdx.x;
+  if (tid == 0 && first < ntiles) {
+    issue(buf_adv, &m_adv, bars + 0, first);
+    issue(buf_w, &m_w, bars + 2, first);
+    if (use_h) issue(buf_h, &m_h, bars + 1, first);
+  }
+
+  uint32_t it = 0;
+  for (int tile = first; tile < ntiles; tile += gridDim.x, ++it) {
+    const uint32_t par = it & 1u;
+    const int b = tile / TILES, tx = tile - b * TILES;
+    const int q = tx * TC + c;
+    const bool special = (tx == 0);  // CTA-uniform
+    const int next = tile + gridDim.x;
+    const bool has_next = next < ntiles;
+    const T qf = (T)q;
+    Cx<T>* wmain = a.wmain + b * plane + q;
+    Cx<T>* hmain = a.hmain + b * plane + q;
+    Cx<T>* wnyq = a.wnyq + (size_t)b * N;
+    Cx<T>* hnyq = a.hnyq + (size_t)b * N;
+    const Cx<T>* G = a.G + (size_t)b * (MH + 1);
+    Cx<T> g0 = mk<T>((T)0, (T)0);
+    if (t == 0) g0 = ldc(G + q);  // forcing + control, row kx = 0 (needed after the FFT)
+
+    Cx<T> v[E], w[E];
+    mbar_wait(bars + 0, par);
+#pragma unroll
+    for (int m = 0; m < E; ++m) v[m] = ldc(buf_adv + (size_t)(t + TPF * m) * TC + c);
+    __syncthreads();  // all rows are in registers before buf_adv becomes the exchange buffer
+    ColEx<T, TC> exA{buf_adv, c};
+    fft_regs<P, -1, T>(v, s_tw, t, exA);
+
+    if (special) {
+      // unpack column 0: A0[kx] = (W[kx] + conj(W[-kx]))/2, An[kx] = (W[kx] - conj(W[-kx]))/(2i)
+      if (c == 0) {
+#pragma unroll
+        for (int m = 0; m < E; ++m) stc(buf_adv + t + TPF * m, v[m]);
+      }
+      __syncthreads();
+      nyquist_column_update<T, N>(a, buf_adv, s_nyq, hnyq, wnyq, G, use_h, tid, TPF * TC);
+      if (c == 0) {
+#pragma unroll
+        for (int m = 0; m < E; ++m)
+          v[m] = (T)0.5 * (v[m] + conj(ldc(buf_adv + ((N - (t + TPF * m)) & (N - 1)))));
+      }
+      __syncthreads();
+    }
+    if (tid == 0 && has_next) {  // buf_adv is free: prefetch the next tile's advection rows
+      fence_proxy_async();
+      issue(buf_adv, &m_adv, bars + 0, next);
+    }
+
+    if (use_h) mbar_wait(bars + 1, par);
+    mbar_wait(bars + 2, par);
+    constexpr int kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3;
+#pragma unroll
+    for (int m = 0; m < E; ++m) {
+      const int kx = t + TPF * m;
+      const size_t off = (size_t)kx * MH;
+      const int so = kx * TC + c;
+      Cx<T> h = v[m];
+      if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) h = mk<T>((T)0, (T)0);
+      if (m == 0) h = h + g0;
+      if (use_h) h = h + a.beta * ldc(buf_h + so);
+      stc(hmain + off, h);
+      const T p = wave_p<T, P>(tf, m);
+      const T lk = a.munu * (p * p + qf * qf);
+      const Cx<T> wv = ldc(buf_w + so);
+      w[m] = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
+      stc(wmain + off, w[m]);
+    }
+    __syncthreads();  // buf_h and buf_w have been consumed
+    if (tid == 0 && has_next) {
+      fence_proxy_async();
+      issue(buf_w, &m_w, bars + 2, next);
+    }
+
+    ColEx<T, TC> exH{buf_h, c};
+    col_field<0, T, P, TC>(a, w, s_tw, s_nyq, buf_h, exH, c, t, q, b, special);
+    col_field<1, T, P, TC>(a, w, s_tw, s_nyq, buf_h, exH, c, t, q, b, special);
+    col_field<2, T, P, TC>(a, w, s_tw, s_nyq, buf_h, exH, c, t, q, b, special);
+    col_field<3, T, P, TC>(a, w, s_tw, s_nyq, buf_h, exH, c, t, q, b, special);
+    if (tid == 0 && has_next && use_h) {  // every thread is past the last exchange: buf_h is free
+      fence_proxy_async();
+      issue(buf_h, &m_h, bars + 1, next);
+    }
+  }
+}
+
+}  // namespace kf

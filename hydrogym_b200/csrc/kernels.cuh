@@ -57,7 +57,8 @@ template <typename T, int TPF> struct RowEx {
 
 // 1/x: MUFU.RCP + one Newton step for fp32 (branch-free, ~1 ulp); IEEE division for fp64
 __device__ __forceinline__ float fast_rcp(float x) {
-  float r = __fdividef(1.0f, x);
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return fmaf(r, fmaf(-x, r, 1.0f), r);
 }
 __device__ __forceinline__ double fast_rcp(double x) { return 1.0 / x; }
@@ -74,8 +75,33 @@ template <int F, typename T> __device__ __forceinline__ T field_coef(T sp, T sq,
   return F == 0 ? sq * ik2 : F == 1 ? -(sp * ik2) : F == 2 ? sp : sq;
 }
 template <typename T> __device__ __forceinline__ T inv_k2(T p, T q) {
-  const T k2 = p * p + q * q;
-  return k2 > (T)0 ? fast_rcp(k2) : (T)0;
+  // k2 is an integer >= 1 except at p = q = 0, where the coefficient it scales is 0 anyway
+  return fast_rcp(fmax(p * p + q * q, (T)1));
+}
+
+// ky = M/2 column of a tile-0 CTA, all threads cooperating (one kx per thread): unpack
+// An[kx] = (W[kx] - conj(W[-kx]))/(2i) from the packed forward transform W (in s_w[0..N)),
+// then the same RK accumulate + Crank-Nicolson update as the main columns.  New omega_hat
+// values go to global memory and to s_nyq for the prologue.
+template <typename T, int N>
+__device__ __forceinline__ void nyquist_column_update(const StageArgs<T>& a, const Cx<T>* s_w, Cx<T>* s_nyq,
+                                                      Cx<T>* hnyq, Cx<T>* wnyq, const Cx<T>* G, bool use_h,
+                                                      int tid, int nthreads) {
+  constexpr int MH = N / 2;
+  for (int kx = tid; kx < N; kx += nthreads) {
+    const Cx<T> d = ldc(s_w + kx) - conj(ldc(s_w + ((N - kx) & (N - 1))));
+    Cx<T> h = mk<T>((T)0.5 * d.y, (T)-0.5 * d.x);
+    if (a.dealias) h = mk<T>((T)0, (T)0);  // ky = M/2 >= km always
+    if (kx == 0) h = h + ldc(G + MH);
+    if (use_h) h = h + a.beta * ldc(hnyq + kx);
+    stc(hnyq + kx, h);
+    const T p = (T)(kx < N / 2 ? kx : kx - N);
+    const T lk = a.munu * (p * p + (T)MH * (T)MH);
+    Cx<T> wv = ldc(wnyq + kx);
+    wv = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
+    stc(wnyq + kx, wv);
+    stc(s_nyq + kx, wv);
+  }
 }
 
 enum ColMode { kColStage = 0, kColInit = 1, kColObs = 2 };
@@ -174,26 +200,11 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
         for (int m = 0; m < E; ++m) stc(s_ex + t + TPF * m, v[m]);
       }
       __syncthreads();
+      nyquist_column_update<T, N>(a, s_ex, s_nyq, hnyq, wnyq, G, use_h, threadIdx.x, TPF * TC);
       if (c == 0) {
 #pragma unroll
-        for (int m = 0; m < E; ++m) {
-          const int kx = t + TPF * m;
-          const Cx<T> wm = conj(ldc(s_ex + ((N - kx) & (N - 1))));
-          const Cx<T> d = v[m] - wm;
-          v[m] = (T)0.5 * (v[m] + wm);
-          Cx<T> nl = mk<T>((T)0.5 * d.y, (T)-0.5 * d.x);
-          if (a.dealias) nl = mk<T>((T)0, (T)0);  // ky = M/2 >= km always
-          if (kx == 0) nl = nl + ldc(G + MH);
-          Cx<T> h = nl;
-          if (use_h) h = h + a.beta * ldc(hnyq + kx);
-          stc(hnyq + kx, h);
-          const T p = wave_p<T, P>(tf, m);
-          const T lk = a.munu * (p * p + (T)MH * (T)MH);
-          Cx<T> wv = ldc(wnyq + kx);
-          wv = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
-          stc(wnyq + kx, wv);
-          stc(s_nyq + kx, wv);
-        }
+        for (int m = 0; m < E; ++m)
+          v[m] = (T)0.5 * (v[m] + conj(ldc(s_ex + ((N - (t + TPF * m)) & (N - 1)))));
       }
       __syncthreads();
     }

@@ -5,12 +5,13 @@
 #include <cuda_runtime.h>
 
 #include <cmath>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <string>
 #include <vector>
 
-#include "kernels.cuh"
+#include "col_tma.cuh"
 
 namespace {
 
@@ -43,6 +44,9 @@ struct Ops {
   int tc, col_threads, row_groups, row_threads;
   size_t col_smem, row_smem;
   cudaError_t (*prepare)();
+  // TMA-fed persistent column kernel of the RK sub-stage: set-up (tensor maps, grid) and launch
+  int (*tma_setup)(struct Ctx&);
+  void (*col_tma)(const struct Ctx&, int nb, const Stage&, cudaStream_t);
   // all of these work on the chunk-local workspace; nb = environments in the chunk
   void (*col)(const struct Ctx&, int nb, const Stage&, int mode, cudaStream_t);
   void (*row)(const struct Ctx&, int nb, cudaStream_t);
@@ -71,6 +75,10 @@ struct Ctx {
   size_t bytes = 0;
   long long launches = 0;
   bool have_constants = false;
+  // TMA column kernel: tensor maps over advx / hmain / wmain and the persistent grid size
+  CUtensorMap tm_adv, tm_h, tm_w;
+  bool use_tma = false;
+  int tma_ctas = 0;
   // CUDA graph of `graph_steps` RK steps on a full chunk
   cudaGraphExec_t graph = nullptr;
   int graph_steps = 0;
@@ -79,7 +87,7 @@ struct Ctx {
 
 // TC: columns per column-kernel CTA; GROUPS: FFT groups per row-kernel CTA;
 // CB / RB: __launch_bounds__ min-blocks (register caps) of the column / row kernels.
-template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1> struct Impl {
+template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int TB = 1> struct Impl {
   using C = kf::Cx<T>;
   static constexpr int N = P::L, MH = N / 2;
   static size_t col_smem() { return sizeof(C) * (2 * (size_t)N + (size_t)N * TC); }
@@ -149,27 +157,82 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1> struc
     kf::forcing_row_kernel<T><<<dim3((MH + 1 + 127) / 128, nb), 128, 0, s>>>(
         (C*)c.G, (const C*)c.F, (const C*)c.C, (const T*)actions, (T)c.cfg.min_action, (T)c.cfg.max_action, MH + 1);
   }
+  static int tma_setup(Ctx& c);
+  static void col_tma(const Ctx& c, int nb, const Stage& st, cudaStream_t s) {
+    kf::StageArgs<T> a = args(c);
+    a.beta = (T)st.beta; a.gdt = (T)st.gdt; a.munu = (T)st.munu;
+    const int ntiles = nb * (MH / TC);
+    const int grid = ntiles < c.tma_ctas ? ntiles : c.tma_ctas;
+    kf::col_tma_kernel<T, P, TC, TB><<<grid, P::TPF * TC, kf::ColTmaSmem<T, P, TC>::bytes(), s>>>(
+        a, c.tm_adv, c.tm_h, c.tm_w, ntiles);
+  }
   static Ops make() {
     Ops o;
     o.elem = sizeof(C);
     o.tc = TC; o.col_threads = P::TPF * TC; o.row_groups = GROUPS; o.row_threads = P::TPF * GROUPS;
     o.col_smem = col_smem(); o.row_smem = row_smem();
-    o.prepare = prepare; o.col = col; o.row = row; o.obs = obs; o.finalize = finalize;
+    o.prepare = prepare; o.tma_setup = tma_setup; o.col_tma = col_tma; o.col = col; o.row = row; o.obs = obs; o.finalize = finalize;
     o.import_ = import_; o.export_ = export_; o.forcing = forcing;
     return o;
   }
 };
 
+// cuTensorMapEncodeTiled, fetched through the runtime so that the library has no link-time
+// dependency on libcuda (it must load on GPU-less build hosts).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+template <typename T, class P, int TC, int GROUPS, int CB, int RB, int TB>
+int Impl<T, P, TC, GROUPS, CB, RB, TB>::tma_setup(Ctx& c) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return fail("cuTensorMapEncodeTiled is not available from this driver");
+  const size_t smem = kf::ColTmaSmem<T, P, TC>::bytes();
+  auto kern = kf::col_tma_kernel<T, P, TC, TB>;
+  KF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0, sms = 0;
+  KF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, P::TPF * TC, smem));
+  KF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.cfg.device));
+  if (per_sm < 1) return fail("col_tma_kernel does not fit on an SM");
+  c.tma_ctas = per_sm * sms;
+  const CUtensorMapDataType dt = sizeof(T) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64;
+  const cuuint64_t dims[2] = {(cuuint64_t)(2 * MH), (cuuint64_t)c.chunk * N};
+  const cuuint64_t strides[1] = {(cuuint64_t)(2 * MH) * sizeof(T)};
+  const cuuint32_t box[2] = {(cuuint32_t)(2 * TC), (cuuint32_t)(N < 256 ? N : 256)};
+  const cuuint32_t estr[2] = {1, 1};
+  void* bases[3] = {c.advx, c.hmain, c.wmain};
+  CUtensorMap* maps[3] = {&c.tm_adv, &c.tm_h, &c.tm_w};
+  for (int i = 0; i < 3; ++i) {
+    CUresult r = enc(maps[i], dt, 2, bases[i], dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+  }
+  c.use_tma = true;
+  return 0;
+}
+
 const Ops* find_ops(int dtype, int N) {
   using kf::Plan;
   static const Ops f64_[] = {Impl<float, Plan<64, 8, 8, 8>, 16, 16>::make()};
   static const Ops f128[] = {Impl<float, Plan<128, 8, 16, 8>, 16, 16>::make()};
-  static const Ops f256[] = {Impl<float, Plan<256, 16, 16, 16>, 16, 8, 3, 4>::make()};
+  static const Ops f256[] = {Impl<float, Plan<256, 16, 16, 16>, 16, 8, 3, 4, 2>::make()};
   static const Ops f512[] = {Impl<float, Plan<512, 32, 8, 8, 8>, 8, 4>::make()};
   static const Ops f1024[] = {Impl<float, Plan<1024, 64, 16, 4, 16>, 8, 2>::make()};
   static const Ops d64[] = {Impl<double, Plan<64, 8, 8, 8>, 16, 16>::make()};
   static const Ops d128[] = {Impl<double, Plan<128, 16, 8, 2, 8>, 8, 8>::make()};
-  static const Ops d256[] = {Impl<double, Plan<256, 32, 8, 4, 8>, 8, 4, 3, 4>::make()};
+  static const Ops d256[] = {Impl<double, Plan<256, 32, 8, 4, 8>, 8, 4, 3, 4, 2>::make()};
   static const Ops d512[] = {Impl<double, Plan<512, 64, 8, 8, 8>, 4, 2>::make()};
   static const Ops d1024[] = {Impl<double, Plan<1024, 128, 8, 2, 8, 8>, 4, 1>::make()};
   const bool f = dtype == KF_F32;
@@ -200,7 +263,8 @@ Stage stage_of(const Ctx& c, int s) {
 void enqueue_rk_step(Ctx& c, int nb, cudaStream_t s) {
   for (int k = 0; k < 5; ++k) {
     c.ops->row(c, nb, s);
-    c.ops->col(c, nb, stage_of(c, k), kf::kColStage, s);
+    if (c.use_tma) c.ops->col_tma(c, nb, stage_of(c, k), s);
+    else c.ops->col(c, nb, stage_of(c, k), kf::kColStage, s);
   }
 }
 
@@ -400,6 +464,7 @@ int kf_create(kf_handle* out, const kf_config* cfg) {
     }
     if (e != cudaSuccess) rc = fail(std::string("twiddle upload: ") + cudaGetErrorString(e));
   }
+  if (!rc && !std::getenv("KF_NO_TMA")) rc = ops->tma_setup(c);
   if (rc) {
     free_all(c);
     delete h;
@@ -549,7 +614,10 @@ int kf_profile_kernels(kf_handle h, int reps, float* ms_col, float* ms_row, void
     c.ops->col(c, nb, stage_of(c, 1), kf::kColStage, s);
   }
   KF_CUDA(cudaEventRecord(e0, s));
-  for (int i = 0; i < reps; ++i) c.ops->col(c, nb, stage_of(c, 1 + i % 4), kf::kColStage, s);
+  for (int i = 0; i < reps; ++i) {
+    if (c.use_tma) c.ops->col_tma(c, nb, stage_of(c, 1 + i % 4), s);
+    else c.ops->col(c, nb, stage_of(c, 1 + i % 4), kf::kColStage, s);
+  }
   KF_CUDA(cudaEventRecord(e1, s));
   for (int i = 0; i < reps; ++i) c.ops->row(c, nb, s);
   KF_CUDA(cudaEventRecord(e2, s));

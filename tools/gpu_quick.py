@@ -22,6 +22,8 @@ def run(N, B, dtype, steps=20, **kw):
     C = N * (N // 2 + 1) * w_bytes
     gbs = 70 * C * B / (ms * 1e-3) / 1e9
     print(f"N={N} B={B} {dtype} {kw}: {ms:.3f} ms/RK-step  {B/ms*1e3:.0f} RKsteps*env/s  alg {gbs:.0f} GB/s ({gbs/6545*100:.1f}%) finite={bool(torch.isfinite(torch.view_as_real(w)).all())}", flush=True)
+    mc, mr = st.profile_kernels(20)
+    print(f"      col {mc*1e3:.1f} us  row {mr*1e3:.1f} us per launch (chunk {st.chunk})", flush=True)
     st.close()
 
 if __name__ == "__main__":
