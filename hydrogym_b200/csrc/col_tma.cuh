@@ -7,13 +7,17 @@
 //
 //   buffer   filled by TMA with     consumed by                      then reused as
 //   buf_adv  adv rows of tile i     first FFT pass (registers)       exchange buffer of the forward FFT
-//   buf_h    h of tile i            RK accumulate                    exchange buffer of the 4 inverse FFTs
-//   buf_w    omega_hat of tile i    Crank-Nicolson update            --
+//   buf_h    h of tile i            RK accumulate                    split exchange buffer of the two lane-paired
+//                                                                    inverse FFTs (real, then imaginary parts)
+//   buf_w    omega_hat of tile i    Crank-Nicolson update            the NEW omega_hat, read back by the prologue
+//                                                                    (keeps 2*E registers free for the paired FFT)
 //
 // As soon as a buffer's last reader has passed a barrier, thread 0 re-arms its mbarrier and
 // issues the load of the NEXT tile of this CTA (tile + gridDim.x): adv right after the forward
-// FFT, omega_hat after the update, h after the last inverse FFT.  Outputs leave with plain
-// coalesced stores.  One CTA = TPF*TC threads; grid = (#SMs x resident CTAs), tiles round-robin.
+// FFT (it is needed first), h and omega_hat after the last inverse FFT (they are needed only
+// after the next tile's forward FFT, which is longer than a TMA round trip).  Outputs leave with
+// plain coalesced stores (128-bit for the lane-paired fields).  One CTA = TPF*TC threads;
+// grid = (#SMs x resident CTAs), tiles round-robin.
 #pragma once
 #include <cuda.h>  // CUtensorMap (type only; the encoder is fetched at run time)
 
@@ -56,6 +60,7 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
 template <typename T, class P, int TC> struct ColTmaSmem {
   static constexpr int N = P::L;
   static constexpr size_t kTile = (size_t)N * TC * sizeof(Cx<T>);
+  static_assert(kTile == col_exchange_bytes<T, N, TC>(), "a tile buffer doubles as the exchange buffer");
   static constexpr size_t bytes() { return 3 * kTile + 2 * (size_t)N * sizeof(Cx<T>) + 64; }
 };
 
@@ -74,7 +79,6 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
   Cx<T>* s_nyq = s_tw + N;
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_nyq + N);  // [0] adv, [1] h, [2] w
   const int tid = threadIdx.x, c = tid % TC, t = tid / TC;
-  const T tf = (T)t;
   const bool use_h = (a.beta != (T)0);
   const size_t plane = (size_t)N * MH;
 
@@ -87,8 +91,17 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
   for (int i = tid; i < N; i += TPF * TC) s_tw[i] = ldc(a.tw + i);
   __syncthreads();
 
+  // Work list: the nb tiles with tx == 0 first (they also carry the ky = M/2 column and cost more), then
+  // the others.  CTA i takes positions i, i + gridDim.x, ...: every CTA gets at most one expensive tile
+  // instead of the same few CTAs getting all of them (gridDim.x is often a multiple of TILES).
+  const int nb = ntiles / TILES;
+  auto decode = [&](int pos, int& b, int& tx) {
+    if (pos < nb) { b = pos; tx = 0; }
+    else { constexpr int TM1 = TILES > 1 ? TILES - 1 : 1; const int r = pos - nb; b = r / TM1; tx = 1 + (r - b * TM1); }
+  };
   auto issue = [&](Cx<T>* buf, const CUtensorMap* map, uint64_t* bar, int tile) {
-    const int b = tile / TILES, tx = tile - b * TILES;
+    int b, tx;
+    decode(tile, b, tx);
     mbar_expect_tx(bar, kBytes);
 #pragma unroll
     for (int r = 0; r < NBOX; ++r)
@@ -105,12 +118,12 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
   uint32_t it = 0;
   for (int tile = first; tile < ntiles; tile += gridDim.x, ++it) {
     const uint32_t par = it & 1u;
-    const int b = tile / TILES, tx = tile - b * TILES;
+    int b, tx;
+    decode(tile, b, tx);
     const int q = tx * TC + c;
     const bool special = (tx == 0);  // CTA-uniform
     const int next = tile + gridDim.x;
     const bool has_next = next < ntiles;
-    const T qf = (T)q;
     Cx<T>* wmain = a.wmain + b * plane + q;
     Cx<T>* hmain = a.hmain + b * plane + q;
     Cx<T>* wnyq = a.wnyq + (size_t)b * N;
@@ -119,7 +132,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     Cx<T> g0 = mk<T>((T)0, (T)0);
     if (t == 0) g0 = ldc(G + q);  // forcing + control, row kx = 0 (needed after the FFT)
 
-    Cx<T> v[E], w[E];
+    Cx<T> v[E];
     mbar_wait(bars + 0, par);
 #pragma unroll
     for (int m = 0; m < E; ++m) v[m] = ldc(buf_adv + (size_t)(t + TPF * m) * TC + c);
@@ -138,7 +151,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
       if (c == 0) {
 #pragma unroll
         for (int m = 0; m < E; ++m)
-          v[m] = (T)0.5 * (v[m] + conj(ldc(buf_adv + ((N - (t + TPF * m)) & (N - 1)))));
+          v[m] = (T)0.5 * add_conj(v[m], ldc(buf_adv + ((N - (t + TPF * m)) & (N - 1))));
       }
       __syncthreads();
     }
@@ -149,37 +162,23 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
 
     if (use_h) mbar_wait(bars + 1, par);
     mbar_wait(bars + 2, par);
-    constexpr int kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3;
+    Cx<T> w[E];
+    rk_update_column<T, P>(a, v, w, g0, use_h, t, q, hmain, wmain,
+                           [&](int, int kx) { return ldc(buf_h + kx * TC + c); },
+                           [&](int, int kx) { return ldc(buf_w + kx * TC + c); });
+    // the new omega_hat replaces the old one in buf_w (each thread rewrites exactly what it read)
 #pragma unroll
-    for (int m = 0; m < E; ++m) {
-      const int kx = t + TPF * m;
-      const size_t off = (size_t)kx * MH;
-      const int so = kx * TC + c;
-      Cx<T> h = v[m];
-      if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) h = mk<T>((T)0, (T)0);
-      if (m == 0) h = h + g0;
-      if (use_h) h = h + a.beta * ldc(buf_h + so);
-      stc(hmain + off, h);
-      const T p = wave_p<T, P>(tf, m);
-      const T lk = a.munu * (p * p + qf * qf);
-      const Cx<T> wv = ldc(buf_w + so);
-      w[m] = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
-      stc(wmain + off, w[m]);
-    }
-    __syncthreads();  // buf_h and buf_w have been consumed
+    for (int m = 0; m < E; ++m) stc(buf_w + (t + TPF * m) * TC + c, w[m]);
+    __syncthreads();  // buf_h has been consumed and becomes the exchange buffer
+
+    auto load_w = [&](int, int kx) { return ldc(buf_w + kx * TC + c); };
+    col_field_pair<0, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
+    col_field_pair<1, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
+    __syncthreads();  // every thread has read its omega_hat for the second pair
     if (tid == 0 && has_next) {
       fence_proxy_async();
+      if (use_h) issue(buf_h, &m_h, bars + 1, next);
       issue(buf_w, &m_w, bars + 2, next);
-    }
-
-    ColEx<T, TC> exH{buf_h, c};
-    col_field<0, T, P, TC>(a, w, s_tw, s_nyq, buf_h, exH, c, t, q, b, special);
-    col_field<1, T, P, TC>(a, w, s_tw, s_nyq, buf_h, exH, c, t, q, b, special);
-    col_field<2, T, P, TC>(a, w, s_tw, s_nyq, buf_h, exH, c, t, q, b, special);
-    col_field<3, T, P, TC>(a, w, s_tw, s_nyq, buf_h, exH, c, t, q, b, special);
-    if (tid == 0 && has_next && use_h) {  // every thread is past the last exchange: buf_h is free
-      fence_proxy_async();
-      issue(buf_h, &m_h, bars + 1, next);
     }
   }
 }

@@ -11,10 +11,15 @@
 //
 // Layouts (per environment):
 //   spectral  omega_hat, h : main[N][M/2] (ky = 0..M/2-1) + nyq[N] (ky = M/2)
-//   x-space   fields, adv  : [N][M/2] complex with column 0 PACKED as
+//   x-space   adv          : [N][M/2] complex with column 0 PACKED as
 //             Re(column ky=0) + i*Re(column ky=M/2): irfftn drops the imaginary
 //             part of those two columns after the x-transform, and rfftn's y-pass
 //             makes them real, so one complex column carries both.
+//   x-space   fields       : two arrays FA, FB of [N][M/2] LANE-PAIRED complex
+//             numbers (re0, re1, im0, im1): FA carries (u_hat, gx_hat), FB carries
+//             (v_hat, gy_hat), column 0 packed as above.  The pairs share every
+//             twiddle, so the inverse x- and y-FFTs run two transforms per
+//             instruction (F2 lanes: FFMA2 / FADD2 / FMUL2) with 128-bit accesses.
 // Wavenumbers are the integers p = fftfreq index, q = rfftfreq index (2*pi*kx = p).
 #pragma once
 #include "fft.cuh"
@@ -22,14 +27,15 @@
 namespace kf {
 
 template <typename T> struct StageArgs {
+  using L2 = typename PairOf<T>::type;
   Cx<T>* wmain;        // [Bc][N][M/2]
   Cx<T>* wnyq;         // [Bc][N]
   Cx<T>* hmain;        // [Bc][N][M/2]
   Cx<T>* hnyq;         // [Bc][N]
   const Cx<T>* G;      // [Bc][M/2+1]  forcing + control row (kx = 0)
   Cx<T>* advx;         // [Bc][N][M/2] packed x-space advection
-  Cx<T>* fld;          // [4][Bc][N][M/2] packed x-space u, v, gx, gy
-  size_t fstride;      // elements between fields
+  Cx<L2>* fa;          // [Bc][N][M/2] lanes (u_hat, gx_hat) in x-space
+  Cx<L2>* fb;          // [Bc][N][M/2] lanes (v_hat, gy_hat) in x-space
   const Cx<T>* tw;     // [N] exp(-2*pi*i*m/N)
   T beta, gdt, munu;   // beta_s, gamma_s*dt, mu_s*nu
   T scale;             // 1/(N*M), folded into the prologue
@@ -37,19 +43,30 @@ template <typename T> struct StageArgs {
 };
 
 // exchange policy of the column kernel: TC columns interleaved, conflict-free
-template <typename T, int TC> struct ColEx {
-  Cx<T>* sm; int c;
-  __device__ __forceinline__ void store(int pos, Cx<T> a) { stc(sm + pos * TC + c, a); }
-  __device__ __forceinline__ Cx<T> load(int pos) { return ldc(sm + pos * TC + c); }
+template <typename X, int TC> struct ColEx {
+  static constexpr bool kSplit = false;
+  Cx<X>* sm; int c;
+  __device__ __forceinline__ void store(int pos, Cx<X> a) { stc(sm + pos * TC + c, a); }
+  __device__ __forceinline__ Cx<X> load(int pos) { return ldc(sm + pos * TC + c); }
+  __device__ __forceinline__ void sync() { __syncthreads(); }
+};
+
+// split variant for lane-paired data: real parts, then imaginary parts, through N x TC lane values
+template <typename X, int TC> struct ColExSplit {
+  static constexpr bool kSplit = true;
+  X* sm; int c;
+  __device__ __forceinline__ void store_part(int pos, X a) { stl(sm + pos * TC + c, a); }
+  __device__ __forceinline__ X load_part(int pos) { return ldl(sm + pos * TC + c); }
   __device__ __forceinline__ void sync() { __syncthreads(); }
 };
 
 // exchange policy of the row kernels: one padded buffer per FFT group
-template <typename T, int TPF> struct RowEx {
-  Cx<T>* sm;
+template <typename X, int TPF> struct RowEx {
+  static constexpr bool kSplit = false;
+  Cx<X>* sm;
   __device__ __forceinline__ static int pad(int pos) { return pos + (pos >> 4); }
-  __device__ __forceinline__ void store(int pos, Cx<T> a) { stc(sm + pad(pos), a); }
-  __device__ __forceinline__ Cx<T> load(int pos) { return ldc(sm + pad(pos)); }
+  __device__ __forceinline__ void store(int pos, Cx<X> a) { stc(sm + pad(pos), a); }
+  __device__ __forceinline__ Cx<X> load(int pos) { return ldc(sm + pad(pos)); }
   __device__ __forceinline__ void sync() {
     if (TPF <= 32) __syncwarp(); else __syncthreads();
   }
@@ -68,15 +85,24 @@ template <typename T, class P> __device__ __forceinline__ T wave_p(T tf, int m) 
   return tf + (T)(P::TPF * m - (m >= P::E / 2 ? P::L : 0));
 }
 
-// coefficient c with field_hat = c * (i * omega_hat) given sp = p*scale, sq = q*scale, ik2 = 1/(p^2+q^2)
-// (0 at p=q=0).  F: 0 u_hat = i q w / k^2, 1 v_hat = -i p w / k^2, 2 gx_hat = i p w, 3 gy_hat = i q w
-// (kolmogorov.py:236-246 with 2*pi*kx = p, 2*pi*ky = q).
-template <int F, typename T> __device__ __forceinline__ T field_coef(T sp, T sq, T ik2) {
-  return F == 0 ? sq * ik2 : F == 1 ? -(sp * ik2) : F == 2 ? sp : sq;
-}
 template <typename T> __device__ __forceinline__ T inv_k2(T p, T q) {
   // k2 is an integer >= 1 except at p = q = 0, where the coefficient it scales is 0 anyway
   return fast_rcp(fmax(p * p + q * q, (T)1));
+}
+
+// Lane-paired coefficients c with field_hat = c * (i * omega_hat), given the integer wavenumbers p, q
+// (kolmogorov.py:236-246 with 2*pi*kx = p, 2*pi*ky = q; `scale` = 1/(N*M) of the inverse transform):
+//   PAIR 0: (u_hat = i q w / k^2,  gx_hat = i p w)      PAIR 1: (v_hat = -i p w / k^2,  gy_hat = i q w)
+template <int PAIR, typename T> __device__ __forceinline__ typename PairOf<T>::type pair_coef(T p, T q, T scale) {
+  using L2 = typename PairOf<T>::type;
+  const T sp = p * scale, sq = q * scale, ik2 = inv_k2<T>(p, q);
+  return PAIR == 0 ? L2(sq * ik2, sp) : L2(-(sp * ik2), sq);
+}
+// cf * (i * w) over both lanes
+template <typename T> __device__ __forceinline__ Cx<typename PairOf<T>::type> coef_times_iw(typename PairOf<T>::type cf,
+                                                                                          Cx<T> w) {
+  using L2 = typename PairOf<T>::type;
+  return mk<L2>(cf * bc<L2>(-w.y), cf * bc<L2>(w.x));
 }
 
 // ky = M/2 column of a tile-0 CTA, all threads cooperating (one kx per thread): unpack
@@ -104,41 +130,41 @@ __device__ __forceinline__ void nyquist_column_update(const StageArgs<T>& a, con
   }
 }
 
-enum ColMode { kColStage = 0, kColInit = 1, kColObs = 2 };
+enum ColMode { kColStage = 0, kColInit = 1 };
+
+// Shared-memory bytes of the column kernels' exchange buffer: N x TC scalar complex numbers, which is
+// also N x TC lane PAIRS (the lane-paired FFTs exchange real and imaginary parts in two rounds).
+template <typename T, int N, int TC> __host__ __device__ constexpr size_t col_exchange_bytes() {
+  static_assert(TC >= 4, "the packed-column scratch (2 x N paired complex) must fit in the exchange buffer");
+  return (size_t)N * TC * sizeof(Cx<T>);
+}
 
 // ---------------------------------------------------------------------------
-// Column kernel.  grid = (M/2 / TC, Bc), block = TPF*TC threads; thread (c, t)
-// owns column q = tile*TC + c and rows {t + TPF*m}: every global access is a run
-// of TC consecutive complex numbers per row (128 B for TC=16 complex64).
-// Tile 0 also carries the ky = M/2 column, packed with ky = 0 in x-space.
-//   MODE kColStage : epilogue of a sub-stage + prologue (4 fields) for the next one
-//   MODE kColInit  : prologue only (4 fields) from the stored omega_hat
-//   MODE kColObs   : prologue only, u_hat and v_hat (reward / observation path)
+// Prologue of the NEXT nonlinear term for one column: lane pair PAIR of the four
+// spectral fields of omega_hat (w[] in registers), inverse x-FFT, store to FA/FB.
+// Thread (c, t) owns column q = tile*TC + c and rows {t + TPF*m}.
 // ---------------------------------------------------------------------------
-template <int F, typename T, class P, int TC>
-__device__ __forceinline__ void col_field(const StageArgs<T>& a, const Cx<T>* w, const Cx<T>* s_tw, Cx<T>* s_nyq,
-                                          Cx<T>* s_ex, ColEx<T, TC>& ex, int c, int t, int q, int b, bool special) {
+template <int PAIR, typename T, class P, int TC, class LoadW>
+__device__ __forceinline__ void col_field_pair(const StageArgs<T>& a, LoadW load_w, const Cx<T>* s_tw,
+                                               const Cx<T>* s_nyq, void* s_exchange, int c, int t, int q, int b,
+                                               bool special) {
+  using L2 = typename PairOf<T>::type;
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
-  const T tf = (T)t, sq = (T)q * a.scale;
-  Cx<T> v[E];
+  const T tf = (T)t, qf = (T)q;
+  Cx<L2> v[E];
 #pragma unroll
-  for (int m = 0; m < E; ++m) {
-    const T p = wave_p<T, P>(tf, m);
-    const T cf = field_coef<F, T>(p * a.scale, sq, (F < 2) ? inv_k2<T>(p, (T)q) : (T)0);
-    v[m] = cf * mul_i(w[m]);
-  }
+  for (int m = 0; m < E; ++m)
+    v[m] = coef_times_iw<T>(pair_coef<PAIR, T>(wave_p<T, P>(tf, m), qf, a.scale), load_w(m, t + TPF * m));
   if (special) {
     // column 0 <- herm(field[:,0]) + i*herm(field[:,M/2]); herm(a)[kx] = (a[kx]+conj(a[-kx]))/2
-    Cx<T>* sA = s_ex;
-    Cx<T>* sB = s_ex + N;
+    Cx<L2>* sA = reinterpret_cast<Cx<L2>*>(s_exchange);
+    Cx<L2>* sB = sA + N;
     if (c == 0) {
 #pragma unroll
       for (int m = 0; m < E; ++m) {
         const int kx = t + TPF * m;
-        const T p = wave_p<T, P>(tf, m);
-        const T cf = field_coef<F, T>(p * a.scale, (T)MH * a.scale, (F < 2) ? inv_k2<T>(p, (T)MH) : (T)0);
         stc(sA + kx, v[m]);
-        stc(sB + kx, cf * mul_i(ldc(s_nyq + kx)));
+        stc(sB + kx, coef_times_iw<T>(pair_coef<PAIR, T>(wave_p<T, P>(tf, m), (T)MH, a.scale), ldc(s_nyq + kx)));
       }
     }
     __syncthreads();
@@ -147,31 +173,67 @@ __device__ __forceinline__ void col_field(const StageArgs<T>& a, const Cx<T>* w,
       for (int m = 0; m < E; ++m) {
         const int kx = t + TPF * m;
         const int mkx = (N - kx) & (N - 1);
-        const Cx<T> ah = (T)0.5 * (v[m] + conj(ldc(sA + mkx)));
-        const Cx<T> bh = (T)0.5 * (ldc(sB + kx) + conj(ldc(sB + mkx)));
-        v[m] = mk<T>(ah.x - bh.y, ah.y + bh.x);
+        const Cx<L2> ah = add_conj(v[m], ldc(sA + mkx));           // 2 * herm(A)
+        const Cx<L2> bh = add_conj(ldc(sB + kx), ldc(sB + mkx));   // 2 * herm(B)
+        v[m] = mk<L2>((ah.x - bh.y) * L2(0.5), (ah.y + bh.x) * L2(0.5));
       }
     }
     __syncthreads();
   }
-  fft_regs<P, +1, T>(v, s_tw, t, ex);
-  Cx<T>* out = a.fld + F * a.fstride + (size_t)b * N * MH + q;
+  ColExSplit<L2, TC> ex{reinterpret_cast<L2*>(s_exchange), c};
+  fft_regs<P, +1, L2>(v, s_tw, t, ex);
+  Cx<L2>* out = (PAIR == 0 ? a.fa : a.fb) + (size_t)b * N * MH + q;
 #pragma unroll
   for (int m = 0; m < E; ++m) stc(out + (size_t)(t + TPF * m) * MH, v[m]);
 }
 
+// RK accumulate + Crank-Nicolson update of one column (S:53-56, K:209-220): v[] holds the forward
+// x-transform of the advection column (column 0 already unpacked), hin/win the old h / omega_hat.
+// Returns the new omega_hat in w[] and stores h, omega_hat to global memory.
+template <typename T, class P, class LoadH, class LoadW>
+__device__ __forceinline__ void rk_update_column(const StageArgs<T>& a, const Cx<T>* v, Cx<T>* w, Cx<T> g0, bool use_h,
+                                                 int t, int q, Cx<T>* hmain, Cx<T>* wmain, LoadH load_h, LoadW load_w) {
+  constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
+  constexpr int kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3;
+  const T tf = (T)t, qf = (T)q;
+#pragma unroll
+  for (int m = 0; m < E; ++m) {
+    const int kx = t + TPF * m;
+    const size_t off = (size_t)kx * MH;
+    Cx<T> h = v[m];
+    if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) h = mk<T>((T)0, (T)0);
+    if (m == 0) h = h + g0;  // g0 is zero except on row kx = 0 (t == 0)
+    if (use_h) h = h + a.beta * load_h(m, kx);
+    stc(hmain + off, h);
+    const T p = wave_p<T, P>(tf, m);
+    const T lk = a.munu * (p * p + qf * qf);
+    const Cx<T> wv = load_w(m, kx);
+    w[m] = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
+    stc(wmain + off, w[m]);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Column kernel (direct-load variant).  grid = (M/2 / TC, Bc), block = TPF*TC threads;
+// every global access is a run of TC consecutive elements per row.  Tile 0 also carries
+// the ky = M/2 column, packed with ky = 0 in x-space.
+//   MODE kColStage : epilogue of a sub-stage + prologue (4 fields) for the next one
+//   MODE kColInit  : prologue only from the stored omega_hat (first stage of a rollout,
+//                    observation of a stored trajectory)
+// The RK sub-stages normally run through col_tma_kernel (col_tma.cuh); this kernel is the
+// KF_NO_TMA fallback and the prologue-only path.
+// ---------------------------------------------------------------------------
 template <typename T, class P, int TC, int MODE, int MINB>
 __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw);
+  Cx<T>* s_sc = reinterpret_cast<Cx<T>*>(smem_raw);  // exchange buffer, scalar-complex view
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + col_exchange_bytes<T, N, TC>());
   Cx<T>* s_nyq = s_tw + N;
-  Cx<T>* s_ex = s_nyq + N;
   const int c = threadIdx.x % TC, t = threadIdx.x / TC;
   const int b = blockIdx.y;
   const int q = blockIdx.x * TC + c;
   const bool special = (blockIdx.x == 0);  // CTA-uniform
-  const T qf = (T)q, tf = (T)t;
   const size_t plane = (size_t)N * MH;
   Cx<T>* wmain = a.wmain + b * plane + q;
   Cx<T>* wnyq = a.wnyq + (size_t)b * N;
@@ -179,9 +241,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
   for (int i = threadIdx.x; i < N; i += TPF * TC) s_tw[i] = ldc(a.tw + i);
   __syncthreads();
 
-  ColEx<T, TC> ex{s_ex, c};
   Cx<T> w[E];
-
   if constexpr (MODE == kColStage) {
     Cx<T>* hmain = a.hmain + b * plane + q;
     Cx<T>* hnyq = a.hnyq + (size_t)b * N;
@@ -191,40 +251,29 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
     Cx<T> v[E];
 #pragma unroll
     for (int m = 0; m < E; ++m) v[m] = ldc(advx + (size_t)(t + TPF * m) * MH);
+    ColEx<T, TC> ex{s_sc, c};
     fft_regs<P, -1, T>(v, s_tw, t, ex);
 
     if (special) {
       // unpack column 0: A0[kx] = (W[kx] + conj(W[-kx]))/2, An[kx] = (W[kx] - conj(W[-kx]))/(2i)
       if (c == 0) {
 #pragma unroll
-        for (int m = 0; m < E; ++m) stc(s_ex + t + TPF * m, v[m]);
+        for (int m = 0; m < E; ++m) stc(s_sc + t + TPF * m, v[m]);
       }
       __syncthreads();
-      nyquist_column_update<T, N>(a, s_ex, s_nyq, hnyq, wnyq, G, use_h, threadIdx.x, TPF * TC);
+      nyquist_column_update<T, N>(a, s_sc, s_nyq, hnyq, wnyq, G, use_h, threadIdx.x, TPF * TC);
       if (c == 0) {
 #pragma unroll
         for (int m = 0; m < E; ++m)
-          v[m] = (T)0.5 * (v[m] + conj(ldc(s_ex + ((N - (t + TPF * m)) & (N - 1)))));
+          v[m] = (T)0.5 * add_conj(v[m], ldc(s_sc + ((N - (t + TPF * m)) & (N - 1))));
       }
       __syncthreads();
     }
-
-    constexpr int kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3;
-#pragma unroll
-    for (int m = 0; m < E; ++m) {
-      const int kx = t + TPF * m;
-      const size_t off = (size_t)kx * MH;
-      Cx<T> h = v[m];
-      if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) h = mk<T>((T)0, (T)0);
-      if (m == 0 && t == 0) h = h + ldc(G + q);
-      if (use_h) h = h + a.beta * ldc(hmain + off);
-      stc(hmain + off, h);
-      const T p = wave_p<T, P>(tf, m);
-      const T lk = a.munu * (p * p + qf * qf);
-      const Cx<T> wv = ldc(wmain + off);
-      w[m] = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
-      stc(wmain + off, w[m]);
-    }
+    Cx<T> g0 = mk<T>((T)0, (T)0);
+    if (t == 0) g0 = ldc(G + q);
+    rk_update_column<T, P>(a, v, w, g0, use_h, t, q, hmain, wmain,
+                           [&](int, int kx) { return ldc(hmain + (size_t)kx * MH); },
+                           [&](int, int kx) { return ldc(wmain + (size_t)kx * MH); });
   } else {
 #pragma unroll
     for (int m = 0; m < E; ++m) w[m] = ldc(wmain + (size_t)(t + TPF * m) * MH);
@@ -234,90 +283,96 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
     }
   }
 
-  col_field<0, T, P, TC>(a, w, s_tw, s_nyq, s_ex, ex, c, t, q, b, special);
-  col_field<1, T, P, TC>(a, w, s_tw, s_nyq, s_ex, ex, c, t, q, b, special);
-  if constexpr (MODE != kColObs) {
-    col_field<2, T, P, TC>(a, w, s_tw, s_nyq, s_ex, ex, c, t, q, b, special);
-    col_field<3, T, P, TC>(a, w, s_tw, s_nyq, s_ex, ex, c, t, q, b, special);
-  }
+  auto load_w = [&](int m, int) { return w[m]; };
+  col_field_pair<0, T, P, TC>(a, load_w, s_tw, s_nyq, s_sc, c, t, q, b, special);
+  col_field_pair<1, T, P, TC>(a, load_w, s_tw, s_nyq, s_sc, c, t, q, b, special);
 }
 
 // ---------------------------------------------------------------------------
-// Row kernels.  A group of TPF threads owns two x-rows (x0, x0+1).  Per row, two
-// complex length-M inverse FFTs give (u + i v) and (gx + i gy) -- two real c2r
-// transforms per complex FFT -- and the two rows' advection values go through
-// ONE forward complex FFT, W = FFT(adv[x0] + i adv[x0+1]), split afterwards by
-// Hermitian symmetry.  Global loads are direct (coalesced both for k and for the
-// mirrored index M-k); the only shared-memory traffic is the FFT exchange.
+// Row kernels.  A group of TPF threads owns two x-rows (x0, x0+1).  Per row ONE
+// lane-paired inverse FFT of length M gives (u + i v) in lane 0 and (gx + i gy) in
+// lane 1 -- four real c2r transforms per paired complex FFT -- and the two rows'
+// advection values go through ONE forward complex FFT, W = FFT(adv[x0] + i adv[x0+1]),
+// split afterwards by Hermitian symmetry.  Global loads are direct (coalesced both
+// for k and for the mirrored index M-k); the only shared-memory traffic is the FFT
+// exchange.
 // ---------------------------------------------------------------------------
 
-// Z[k] = A[k] + i B[k] for the Hermitian extensions of the packed half-rows A, B
-template <typename T, class P>
-__device__ __forceinline__ void load_pair_hermitian(Cx<T>* z, const Cx<T>* __restrict__ A,
-                                                    const Cx<T>* __restrict__ B, int t) {
+// Z[k] = A[k] + i B[k] for the Hermitian extensions of the packed half-rows A, B (any lane type)
+template <typename X, class P>
+__device__ __forceinline__ void load_pair_hermitian(Cx<X>* z, const Cx<X>* __restrict__ A, const Cx<X>* __restrict__ B,
+                                                    int t) {
   constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF;
 #pragma unroll
   for (int m = 0; m < E; ++m) {
     const int k = t + TPF * m;
     if (m < E / 2) {
-      const Cx<T> a = ldc(A + k), b = ldc(B + k);
-      z[m] = (k == 0) ? mk<T>(a.x, b.x) : mk<T>(a.x - b.y, a.y + b.x);
+      const Cx<X> a = ldc(A + k), b = ldc(B + k);
+      const Cx<X> z0 = mk<X>(a.x, b.x), zk = mk<X>(a.x - b.y, a.y + b.x);
+      z[m] = (k == 0) ? z0 : zk;
     } else {
       const int src = (k == MH) ? 0 : M - k;
-      const Cx<T> a = ldc(A + src), b = ldc(B + src);
-      z[m] = (k == MH) ? mk<T>(a.y, b.y) : mk<T>(a.x + b.y, b.x - a.y);
+      const Cx<X> a = ldc(A + src), b = ldc(B + src);
+      const Cx<X> zh = mk<X>(a.y, b.y), zk = mk<X>(a.x + b.y, b.x - a.y);
+      z[m] = (k == MH) ? zh : zk;
     }
   }
 }
 
+template <typename T, int M> __host__ __device__ constexpr size_t row_exchange_elems() { return (size_t)M + M / 16; }
+
 template <typename T, class P, int GROUPS, int MINB>
 __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) row_kernel(StageArgs<T> a) {
+  using L2 = typename PairOf<T>::type;
   constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF, N = M;
-  constexpr int EXN = M + M / 16;
+  constexpr int EXN = (int)row_exchange_elems<T, M>();
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw);
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
-  RowEx<T, TPF> ex{s_tw + M + g * EXN};
-  const int b = blockIdx.y;
+  Cx<L2>* s_ex = reinterpret_cast<Cx<L2>*>(smem_raw) + (size_t)g * EXN;
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
+  RowEx<L2, TPF> ex2{s_ex};
+  RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_ex)};
+  // the column kernel walks the environments in ascending order, so its LAST outputs are the ones
+  // still in L2: start from the last environment
+  const int b = gridDim.y - 1 - blockIdx.y;
   const int x0 = 2 * (blockIdx.x * GROUPS + g);
   const size_t plane = (size_t)N * MH;
 
   for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
   __syncthreads();
 
-  T adv[2][E];
+  Cx<T> v[E];
 #pragma unroll
   for (int rr = 0; rr < 2; ++rr) {
     const size_t roff = b * plane + (size_t)(x0 + rr) * MH;
-    Cx<T> z1[E], z2[E];
-    load_pair_hermitian<T, P>(z1, a.fld + roff, a.fld + a.fstride + roff, t);
-    fft_regs<P, +1, T>(z1, s_tw, t, ex);
-    load_pair_hermitian<T, P>(z2, a.fld + 2 * a.fstride + roff, a.fld + 3 * a.fstride + roff, t);
-    fft_regs<P, +1, T>(z2, s_tw, t, ex);
+    Cx<L2> z[E];
+    load_pair_hermitian<L2, P>(z, a.fa + roff, a.fb + roff, t);
+    fft_regs<P, +1, L2>(z, s_tw, t, ex2);
+    // lanes: z.x = (u, gx), z.y = (v, gy)  ->  adv = -(gx*u + gy*v)   (kolmogorov.py:249)
 #pragma unroll
-    for (int m = 0; m < E; ++m) adv[rr][m] = -(z2[m].x * z1[m].x + z2[m].y * z1[m].y);
+    for (int m = 0; m < E; ++m) {
+      const T adv = -(z[m].x.lo() * z[m].x.hi() + z[m].y.lo() * z[m].y.hi());
+      if (rr == 0) v[m].x = adv; else v[m].y = adv;
+    }
   }
 
-  Cx<T> v[E];
+  fft_regs<P, -1, T>(v, s_tw, t, ex1);
 #pragma unroll
-  for (int m = 0; m < E; ++m) v[m] = mk<T>(adv[0][m], adv[1][m]);
-  fft_regs<P, -1, T>(v, s_tw, t, ex);
-#pragma unroll
-  for (int m = 0; m < E; ++m) ex.store(t + TPF * m, v[m]);
-  ex.sync();
+  for (int m = 0; m < E; ++m) ex1.store(t + TPF * m, v[m]);
+  ex1.sync();
   Cx<T>* o0 = a.advx + b * plane + (size_t)x0 * MH;
   Cx<T>* o1 = o0 + MH;
 #pragma unroll
   for (int m = 0; m < E / 2; ++m) {
     const int k = t + TPF * m;
     if (k == 0) {
-      const Cx<T> wn = ex.load(MH);
+      const Cx<T> wn = ex1.load(MH);
       stc(o0, mk<T>(v[m].x, wn.x));
       stc(o1, mk<T>(v[m].y, wn.y));
     } else {
-      const Cx<T> wm = conj(ex.load(M - k));
-      const Cx<T> d = v[m] - wm;
-      stc(o0 + k, (T)0.5 * (v[m] + wm));
+      const Cx<T> wm = ex1.load(M - k);
+      const Cx<T> s = add_conj(v[m], wm), d = sub_conj(v[m], wm);
+      stc(o0 + k, (T)0.5 * s);
       stc(o1 + k, mk<T>((T)0.5 * d.y, (T)-0.5 * d.x));
     }
   }
@@ -325,14 +380,15 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) row_kernel(StageArgs<T> 
 
 // ---------------------------------------------------------------------------
 // Reward / observation row kernel (reference: compute_tke utils.py:175-194 and
-// _trajectory_mean_obs kolmogorov.py:426-446).  Consumes the x-space u_hat, v_hat
-// fields of one snapshot; per environment accumulates sum u, sum v, sum u^2,
+// _trajectory_mean_obs kolmogorov.py:426-446).  Consumes lane 0 (u_hat, v_hat) of the
+// x-space fields of one snapshot; per environment accumulates sum u, sum v, sum u^2,
 // sum v^2 (fp64, warp-shuffle reduction + one atomic per warp) and adds
 // |velocity| at the obs_size x obs_size strided probes into the running obs mean.
 // ---------------------------------------------------------------------------
 template <typename T> struct ObsArgs {
-  const Cx<T>* fld;    // [2][Bc][N][M/2]
-  size_t fstride;
+  using L2 = typename PairOf<T>::type;
+  const Cx<L2>* fa;    // [Bc][N][M/2]
+  const Cx<L2>* fb;
   const Cx<T>* tw;
   double* acc;         // [Bc][4] for this snapshot (stride acc_stride between envs)
   size_t acc_stride;
@@ -343,12 +399,14 @@ template <typename T> struct ObsArgs {
 
 template <typename T, class P, int GROUPS>
 __global__ void __launch_bounds__(P::TPF* GROUPS) row_obs_kernel(ObsArgs<T> a) {
+  using L2 = typename PairOf<T>::type;
   constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF, N = M;
-  constexpr int EXN = M + M / 16;
+  constexpr int EXN = (int)row_exchange_elems<T, M>();
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw);
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
-  RowEx<T, TPF> ex{s_tw + M + g * EXN};
+  Cx<L2>* s_ex = reinterpret_cast<Cx<L2>*>(smem_raw) + (size_t)g * EXN;
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
+  RowEx<L2, TPF> ex{s_ex};
   const int b = blockIdx.y;
   const int x = blockIdx.x * GROUPS + g;
   const size_t roff = ((size_t)b * N + x) * MH;
@@ -356,23 +414,25 @@ __global__ void __launch_bounds__(P::TPF* GROUPS) row_obs_kernel(ObsArgs<T> a) {
   for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
   __syncthreads();
 
-  Cx<T> z[E];
-  load_pair_hermitian<T, P>(z, a.fld + roff, a.fld + a.fstride + roff, t);
-  fft_regs<P, +1, T>(z, s_tw, t, ex);
+  Cx<L2> z[E];
+  load_pair_hermitian<L2, P>(z, a.fa + roff, a.fb + roff, t);
+  fft_regs<P, +1, L2>(z, s_tw, t, ex);
 
   T su = 0, sv = 0, suu = 0, svv = 0;
 #pragma unroll
   for (int m = 0; m < E; ++m) {
-    su += z[m].x; sv += z[m].y;
-    suu += z[m].x * z[m].x; svv += z[m].y * z[m].y;
+    const T u = z[m].x.lo(), vv = z[m].y.lo();
+    su += u; sv += vv;
+    suu += u * u; svv += vv * vv;
   }
   if (x % a.sx == 0 && x / a.sx < a.nobs) {
 #pragma unroll
     for (int m = 0; m < E; ++m) {
       const int y = t + TPF * m;
       if (y % a.sy == 0 && y / a.sy < a.nobs) {
+        const T u = z[m].x.lo(), vv = z[m].y.lo();
         T* o = a.obs + (size_t)b * a.nobs * a.nobs + (x / a.sx) * a.nobs + y / a.sy;
-        *o += a.obs_w * sqrt(z[m].x * z[m].x + z[m].y * z[m].y);  // single writer per launch
+        *o += a.obs_w * sqrt(u * u + vv * vv);  // single writer per launch
       }
     }
   }
@@ -388,7 +448,6 @@ __global__ void __launch_bounds__(P::TPF* GROUPS) row_obs_kernel(ObsArgs<T> a) {
     for (int i = 0; i < 4; ++i) atomicAdd(acc + i, r[i]);
   }
 }
-
 // mean_tke[b] = mean_j 0.5*(sum((u-U)^2) + sum((v-V)^2))/n^2 ; nonfinite flag
 template <typename T>
 __global__ void tke_finalize_kernel(const double* acc, int B, int nsnap, int N, int M, T* mean_tke, int* nonfinite) {

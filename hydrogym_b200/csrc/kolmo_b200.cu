@@ -90,8 +90,9 @@ struct Ctx {
 template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int TB = 1> struct Impl {
   using C = kf::Cx<T>;
   static constexpr int N = P::L, MH = N / 2;
-  static size_t col_smem() { return sizeof(C) * (2 * (size_t)N + (size_t)N * TC); }
-  static size_t row_smem() { return sizeof(C) * ((size_t)N + (size_t)GROUPS * (N + N / 16)); }
+  using C2 = kf::Cx<typename kf::PairOf<T>::type>;  // lane-paired complex (two transforms per element)
+  static size_t col_smem() { return kf::col_exchange_bytes<T, N, TC>() + sizeof(C) * 2 * (size_t)N; }
+  static size_t row_smem() { return sizeof(C2) * GROUPS * kf::row_exchange_elems<T, N>() + sizeof(C) * (size_t)N; }
 
   static cudaError_t prepare() {
     cudaError_t e;
@@ -99,9 +100,6 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
                              (int)col_smem());
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColInit, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)col_smem());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(kf::col_kernel<T, P, TC, kf::kColObs, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)col_smem());
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kf::row_kernel<T, P, GROUPS, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem());
@@ -113,8 +111,8 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
   static kf::StageArgs<T> args(const Ctx& c) {
     kf::StageArgs<T> a;
     a.wmain = (C*)c.wmain; a.wnyq = (C*)c.wnyq; a.hmain = (C*)c.hmain; a.hnyq = (C*)c.hnyq;
-    a.G = (const C*)c.G; a.advx = (C*)c.advx; a.fld = (C*)c.fld;
-    a.fstride = (size_t)c.chunk * c.plane;
+    a.G = (const C*)c.G; a.advx = (C*)c.advx;
+    a.fa = (C2*)c.fld; a.fb = a.fa + (size_t)c.chunk * c.plane;
     a.tw = (const C*)c.tw;
     a.beta = 0; a.gdt = 0; a.munu = 0;
     a.scale = (T)(1.0 / ((double)N * (double)N));
@@ -127,8 +125,7 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     a.beta = (T)st.beta; a.gdt = (T)st.gdt; a.munu = (T)st.munu;
     const dim3 grid(MH / TC, nb);
     if (mode == kf::kColStage) kf::col_kernel<T, P, TC, kf::kColStage, CB><<<grid, P::TPF * TC, col_smem(), s>>>(a);
-    else if (mode == kf::kColInit) kf::col_kernel<T, P, TC, kf::kColInit, CB><<<grid, P::TPF * TC, col_smem(), s>>>(a);
-    else kf::col_kernel<T, P, TC, kf::kColObs, CB><<<grid, P::TPF * TC, col_smem(), s>>>(a);
+    else kf::col_kernel<T, P, TC, kf::kColInit, CB><<<grid, P::TPF * TC, col_smem(), s>>>(a);
   }
   static void row(const Ctx& c, int nb, cudaStream_t s) {
     kf::StageArgs<T> a = args(c);
@@ -136,7 +133,7 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
   }
   static void obs(const Ctx& c, int nb, double* acc, size_t acc_stride, void* obs_dev, double obs_w, cudaStream_t s) {
     kf::ObsArgs<T> a;
-    a.fld = (const C*)c.fld; a.fstride = (size_t)c.chunk * c.plane; a.tw = (const C*)c.tw;
+    a.fa = (const C2*)c.fld; a.fb = a.fa + (size_t)c.chunk * c.plane; a.tw = (const C*)c.tw;
     a.acc = acc; a.acc_stride = acc_stride; a.obs = (T*)obs_dev;
     a.nobs = obs_dev ? c.cfg.obs_size : 0;
     a.sx = a.sy = N / c.cfg.obs_size;
@@ -223,16 +220,38 @@ int Impl<T, P, TC, GROUPS, CB, RB, TB>::tma_setup(Ctx& c) {
   return 0;
 }
 
+// Tuning knobs of the headline configurations; overridable one by one (-DKF_F256_TC=8 ...) for experiments.
+//   TC: columns per column-kernel CTA   GROUPS: FFT groups per row-kernel CTA
+//   CB / RB / TB: min CTAs per SM (register caps) of col_kernel / row_kernel / col_tma_kernel
+#ifndef KF_F256_TC
+#define KF_F256_TC 8
+#endif
+#ifndef KF_F256_GROUPS
+#define KF_F256_GROUPS 8
+#endif
+#ifndef KF_F256_CB
+#define KF_F256_CB 2
+#endif
+#ifndef KF_F256_RB
+#define KF_F256_RB 4
+#endif
+#ifndef KF_F256_TB
+#define KF_F256_TB 2
+#endif
+#define KF_CFG_F256 KF_F256_TC, KF_F256_GROUPS, KF_F256_CB, KF_F256_RB, KF_F256_TB
+#define KF_CFG_D256 8, 4, 2, 4, 2
+#define KF_CFG_F128 16, 16
+
 const Ops* find_ops(int dtype, int N) {
   using kf::Plan;
   static const Ops f64_[] = {Impl<float, Plan<64, 8, 8, 8>, 16, 16>::make()};
-  static const Ops f128[] = {Impl<float, Plan<128, 8, 16, 8>, 16, 16>::make()};
-  static const Ops f256[] = {Impl<float, Plan<256, 16, 16, 16>, 16, 8, 3, 4, 2>::make()};
+  static const Ops f128[] = {Impl<float, Plan<128, 8, 16, 8>, KF_CFG_F128>::make()};
+  static const Ops f256[] = {Impl<float, Plan<256, 16, 16, 16>, KF_CFG_F256>::make()};
   static const Ops f512[] = {Impl<float, Plan<512, 32, 8, 8, 8>, 8, 4>::make()};
   static const Ops f1024[] = {Impl<float, Plan<1024, 64, 16, 4, 16>, 8, 2>::make()};
   static const Ops d64[] = {Impl<double, Plan<64, 8, 8, 8>, 16, 16>::make()};
   static const Ops d128[] = {Impl<double, Plan<128, 16, 8, 2, 8>, 8, 8>::make()};
-  static const Ops d256[] = {Impl<double, Plan<256, 32, 8, 4, 8>, 8, 4, 3, 4, 2>::make()};
+  static const Ops d256[] = {Impl<double, Plan<256, 32, 8, 4, 8>, KF_CFG_D256>::make()};
   static const Ops d512[] = {Impl<double, Plan<512, 64, 8, 8, 8>, 4, 2>::make()};
   static const Ops d1024[] = {Impl<double, Plan<1024, 128, 8, 2, 8, 8>, 4, 1>::make()};
   const bool f = dtype == KF_F32;
@@ -547,7 +566,7 @@ int kf_reward_obs(kf_handle h, const void* trajectory_dev, int n_snap, void* obs
     for (int j = 0; j < n_snap; ++j) {
       const char* tj = (const char*)trajectory_dev + el * user_env * ((size_t)b0 * n_snap + j);
       c.ops->import_(c, nb, tj, user_env * n_snap, s);
-      c.ops->col(c, nb, stage_of(c, 0), kf::kColObs, s);  // u_hat, v_hat -> x-space
+      c.ops->col(c, nb, stage_of(c, 0), kf::kColInit, s);  // fields of the snapshot -> x-space
       c.ops->obs(c, nb, c.acc + 4 * ((size_t)b0 * n_snap + j), 4 * (size_t)n_snap,
                  obs_dev ? (char*)obs_dev + real * (size_t)b0 * nobs2 : nullptr, 1.0 / n_snap, s);
       c.launches += 3;
