@@ -1,23 +1,24 @@
 // Persistent, TMA-fed column kernel for the RK sub-stage (sm_100a).
 //
-// Same arithmetic as col_kernel<..., kColStage> (kernels.cuh) but the three input tiles of a
-// (environment, 16-column) tile -- advection rows, RK register h, omega_hat -- arrive in shared
-// memory through cp.async.bulk.tensor (TMA, SASS UTMALDG) one tile AHEAD of their use, so the
-// FFT/pointwise phases never wait on a global load:
+// Same arithmetic as col_kernel<..., kColStage> (kernels.cuh), but the three input tiles of a
+// (environment, TC-column) tile -- advection rows, RK register h, omega_hat -- arrive in shared
+// memory through cp.async.bulk.tensor (TMA, SASS UTMALDG) a whole tile AHEAD of their use
+// (STAGES = 2 ring of {adv, h, w} buffers), and the updated h / omega_hat tiles leave through TMA
+// stores (UTMASTG) instead of 8-byte per-thread stores:
 //
-//   buffer   filled by TMA with     consumed by                      then reused as
-//   buf_adv  adv rows of tile i     first FFT pass (registers)       exchange buffer of the forward FFT
-//   buf_h    h of tile i            RK accumulate                    split exchange buffer of the two lane-paired
-//                                                                    inverse FFTs (real, then imaginary parts)
-//   buf_w    omega_hat of tile i    Crank-Nicolson update            the NEW omega_hat, read back by the prologue
-//                                                                    (keeps 2*E registers free for the paired FFT)
+//   buffer    filled by TMA with     consumed by                   then reused as
+//   adv[s]    adv rows of tile i     first FFT pass (registers)    exchange buffer of the forward FFT, then the
+//                                                                  NEW h tile (TMA-stored to global)
+//   h[s]      h of tile i            RK accumulate                 split exchange buffer of the two lane-paired
+//                                                                  inverse FFTs (real, then imaginary parts)
+//   w[s]      omega_hat of tile i    Crank-Nicolson update         the NEW omega_hat tile: TMA-stored to global and
+//                                                                  read back by the prologue of the next stage
 //
-// As soon as a buffer's last reader has passed a barrier, thread 0 re-arms its mbarrier and
-// issues the load of the NEXT tile of this CTA (tile + gridDim.x): adv right after the forward
-// FFT (it is needed first), h and omega_hat after the last inverse FFT (they are needed only
-// after the next tile's forward FFT, which is longer than a TMA round trip).  Outputs leave with
-// plain coalesced stores (128-bit for the lane-paired fields).  One CTA = TPF*TC threads;
-// grid = (#SMs x resident CTAs), tiles round-robin.
+// At the end of tile i thread 0 waits for the two TMA stores to have read their buffers and issues
+// the loads of tile i + 2*gridDim.x into the same stage; tile i + gridDim.x is already resident in
+// the other stage.  With STAGES = 1 (grids too large for two stages) adv is re-issued right after the
+// forward FFT and h / omega_hat after the last inverse FFT.  The lane-paired fields leave with
+// 128-bit coalesced stores.  One CTA = TPF*TC threads; grid = #SMs x resident CTAs.
 #pragma once
 #include <cuda.h>  // CUtensorMap (type only; the encoder is fetched at run time)
 
@@ -57,35 +58,44 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       : "memory");
 }
 
-template <typename T, class P, int TC> struct ColTmaSmem {
+// 2-D tiled TMA store: dense [rows][inner] in smem -> box at (c0, c1); completion through the bulk async-group
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, int c0, int c1, const void* src) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(c0), "r"(c1), "r"(smem_u32(src))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+template <typename T, class P, int TC, int STAGES> struct ColTmaSmem {
   static constexpr int N = P::L;
   static constexpr size_t kTile = (size_t)N * TC * sizeof(Cx<T>);
   static_assert(kTile == col_exchange_bytes<T, N, TC>(), "a tile buffer doubles as the exchange buffer");
-  static constexpr size_t bytes() { return 3 * kTile + 2 * (size_t)N * sizeof(Cx<T>) + 64; }
+  static constexpr size_t bytes() { return 3 * STAGES * kTile + 2 * (size_t)N * sizeof(Cx<T>) + 64; }
 };
 
-template <typename T, class P, int TC, int MINB>
+template <typename T, class P, int TC, int MINB, int STAGES>
 __global__ void __launch_bounds__(P::TPF* TC, MINB)
     col_tma_kernel(StageArgs<T> a, const __grid_constant__ CUtensorMap m_adv, const __grid_constant__ CUtensorMap m_h,
                    const __grid_constant__ CUtensorMap m_w, int ntiles) {
+  static_assert(STAGES == 1 || STAGES == 2, "one or two input stages");
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2, TILES = MH / TC;
   constexpr int RB = N < 256 ? N : 256, NBOX = N / RB;  // TMA box rows (<= 256)
   constexpr uint32_t kBytes = (uint32_t)((size_t)N * TC * sizeof(Cx<T>));
+  constexpr size_t kTileEl = (size_t)N * TC;
   extern __shared__ __align__(1024) unsigned char smem_tma[];
-  Cx<T>* buf_adv = reinterpret_cast<Cx<T>*>(smem_tma);
-  Cx<T>* buf_h = buf_adv + (size_t)N * TC;
-  Cx<T>* buf_w = buf_h + (size_t)N * TC;
-  Cx<T>* s_tw = buf_w + (size_t)N * TC;
+  Cx<T>* bufs = reinterpret_cast<Cx<T>*>(smem_tma);  // [STAGES][3][N*TC]: adv, h, w
+  Cx<T>* s_tw = bufs + 3 * STAGES * kTileEl;
   Cx<T>* s_nyq = s_tw + N;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_nyq + N);  // [0] adv, [1] h, [2] w
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_nyq + N);  // [STAGES][3]: adv, h, w
   const int tid = threadIdx.x, c = tid % TC, t = tid / TC;
   const bool use_h = (a.beta != (T)0);
   const size_t plane = (size_t)N * MH;
 
   if (tid == 0) {
-    mbar_init(bars + 0, 1);
-    mbar_init(bars + 1, 1);
-    mbar_init(bars + 2, 1);
+    for (int i = 0; i < 3 * STAGES; ++i) mbar_init(bars + i, 1);
     fence_mbar_init();
   }
   for (int i = tid; i < N; i += TPF * TC) s_tw[i] = ldc(a.tw + i);
@@ -107,25 +117,35 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     for (int r = 0; r < NBOX; ++r)
       tma_load_2d(buf + (size_t)r * RB * TC, map, tx * TC * 2, b * N + r * RB, bar);
   };
+  auto store_tile = [&](const CUtensorMap* map, const Cx<T>* buf, int b, int tx) {
+#pragma unroll
+    for (int r = 0; r < NBOX; ++r) tma_store_2d(map, tx * TC * 2, b * N + r * RB, buf + (size_t)r * RB * TC);
+  };
 
-  const int first = blockIdx.x;
-  if (tid == 0 && first < ntiles) {
-    issue(buf_adv, &m_adv, bars + 0, first);
-    issue(buf_w, &m_w, bars + 2, first);
-    if (use_h) issue(buf_h, &m_h, bars + 1, first);
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      const int tile = blockIdx.x + s * gridDim.x;
+      if (tile >= ntiles) break;
+      issue(bufs + (3 * s + 0) * kTileEl, &m_adv, bars + 3 * s + 0, tile);
+      if (use_h) issue(bufs + (3 * s + 1) * kTileEl, &m_h, bars + 3 * s + 1, tile);
+      issue(bufs + (3 * s + 2) * kTileEl, &m_w, bars + 3 * s + 2, tile);
+    }
   }
 
   uint32_t it = 0;
-  for (int tile = first; tile < ntiles; tile += gridDim.x, ++it) {
-    const uint32_t par = it & 1u;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    const int s = (STAGES == 2) ? (int)(it & 1u) : 0;
+    const uint32_t par = (STAGES == 2) ? ((it >> 1) & 1u) : (it & 1u);
+    Cx<T>* buf_adv = bufs + (3 * s + 0) * kTileEl;
+    Cx<T>* buf_h = bufs + (3 * s + 1) * kTileEl;
+    Cx<T>* buf_w = bufs + (3 * s + 2) * kTileEl;
+    uint64_t* bar = bars + 3 * s;
     int b, tx;
     decode(tile, b, tx);
     const int q = tx * TC + c;
     const bool special = (tx == 0);  // CTA-uniform
-    const int next = tile + gridDim.x;
+    const int next = tile + STAGES * gridDim.x;  // the tile that will reuse this stage
     const bool has_next = next < ntiles;
-    Cx<T>* wmain = a.wmain + b * plane + q;
-    Cx<T>* hmain = a.hmain + b * plane + q;
     Cx<T>* wnyq = a.wnyq + (size_t)b * N;
     Cx<T>* hnyq = a.hnyq + (size_t)b * N;
     const Cx<T>* G = a.G + (size_t)b * (MH + 1);
@@ -133,7 +153,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     if (t == 0) g0 = ldc(G + q);  // forcing + control, row kx = 0 (needed after the FFT)
 
     Cx<T> v[E];
-    mbar_wait(bars + 0, par);
+    mbar_wait(bar + 0, par);
 #pragma unroll
     for (int m = 0; m < E; ++m) v[m] = ldc(buf_adv + (size_t)(t + TPF * m) * TC + c);
     __syncthreads();  // all rows are in registers before buf_adv becomes the exchange buffer
@@ -155,32 +175,59 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
       }
       __syncthreads();
     }
-    if (tid == 0 && has_next) {  // buf_adv is free: prefetch the next tile's advection rows
+    if (STAGES == 1 && tid == 0 && has_next) {  // single stage: buf_adv is needed first, refill it now
       fence_proxy_async();
-      issue(buf_adv, &m_adv, bars + 0, next);
+      issue(buf_adv, &m_adv, bar + 0, next);
     }
 
-    if (use_h) mbar_wait(bars + 1, par);
-    mbar_wait(bars + 2, par);
-    Cx<T> w[E];
-    rk_update_column<T, P>(a, v, w, g0, use_h, t, q, hmain, wmain,
-                           [&](int, int kx) { return ldc(buf_h + kx * TC + c); },
-                           [&](int, int kx) { return ldc(buf_w + kx * TC + c); });
-    // the new omega_hat replaces the old one in buf_w (each thread rewrites exactly what it read)
-#pragma unroll
-    for (int m = 0; m < E; ++m) stc(buf_w + (t + TPF * m) * TC + c, w[m]);
-    __syncthreads();  // buf_h has been consumed and becomes the exchange buffer
+    if (use_h) mbar_wait(bar + 1, par);
+    mbar_wait(bar + 2, par);
+    {
+      Cx<T> w[E];
+      if constexpr (STAGES == 2) {
+        // new h -> buf_adv, new omega_hat -> buf_w (in place); both tiles leave through TMA stores
+        rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
+                               [&](int, int kx, Cx<T> h) { stc(buf_adv + kx * TC + c, h); },
+                               [&](int, int kx, Cx<T> wn) { stc(buf_w + kx * TC + c, wn); },
+                               [&](int, int kx) { return ldc(buf_h + kx * TC + c); },
+                               [&](int, int kx) { return ldc(buf_w + kx * TC + c); });
+        fence_proxy_async();  // make the generic-proxy writes visible to the TMA engine
+        __syncthreads();      // ... and buf_h has been consumed: it becomes the exchange buffer
+        if (tid == 0) {
+          store_tile(&m_h, buf_adv, b, tx);
+          store_tile(&m_w, buf_w, b, tx);
+          bulk_commit();
+        }
+      } else {
+        Cx<T>* wmain = a.wmain + b * plane + q;
+        Cx<T>* hmain = a.hmain + b * plane + q;
+        rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
+                               [&](int, int kx, Cx<T> h) { stc(hmain + (size_t)kx * MH, h); },
+                               [&](int, int kx, Cx<T> wn) {
+                                 stc(wmain + (size_t)kx * MH, wn);
+                                 stc(buf_w + kx * TC + c, wn);
+                               },
+                               [&](int, int kx) { return ldc(buf_h + kx * TC + c); },
+                               [&](int, int kx) { return ldc(buf_w + kx * TC + c); });
+        __syncthreads();  // buf_h has been consumed and becomes the exchange buffer
+      }
+    }
 
     auto load_w = [&](int, int kx) { return ldc(buf_w + kx * TC + c); };
     col_field_pair<0, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
     col_field_pair<1, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
-    __syncthreads();  // every thread has read its omega_hat for the second pair
+    __syncthreads();  // every thread has read its omega_hat for the second pair and left the last exchange
     if (tid == 0 && has_next) {
+      if (STAGES == 2) {
+        bulk_wait_read0();  // the TMA stores have read buf_adv / buf_w
+        issue(buf_adv, &m_adv, bar + 0, next);
+      }
       fence_proxy_async();
-      if (use_h) issue(buf_h, &m_h, bars + 1, next);
-      issue(buf_w, &m_w, bars + 2, next);
+      if (use_h) issue(buf_h, &m_h, bar + 1, next);
+      issue(buf_w, &m_w, bar + 2, next);
     }
   }
+  if (STAGES == 2 && tid == 0) bulk_wait0();  // all TMA stores have landed before the CTA retires
 }
 
 }  // namespace kf

@@ -188,28 +188,28 @@ __device__ __forceinline__ void col_field_pair(const StageArgs<T>& a, LoadW load
 }
 
 // RK accumulate + Crank-Nicolson update of one column (S:53-56, K:209-220): v[] holds the forward
-// x-transform of the advection column (column 0 already unpacked), hin/win the old h / omega_hat.
-// Returns the new omega_hat in w[] and stores h, omega_hat to global memory.
-template <typename T, class P, class LoadH, class LoadW>
+// x-transform of the advection column (column 0 already unpacked); load_h / load_w fetch the old
+// h / omega_hat of row kx, store_h / store_w dispose of the new ones.  Returns the new omega_hat in w[].
+template <typename T, class P, class StoreH, class StoreW, class LoadH, class LoadW>
 __device__ __forceinline__ void rk_update_column(const StageArgs<T>& a, const Cx<T>* v, Cx<T>* w, Cx<T> g0, bool use_h,
-                                                 int t, int q, Cx<T>* hmain, Cx<T>* wmain, LoadH load_h, LoadW load_w) {
+                                                 int t, int q, StoreH store_h, StoreW store_w, LoadH load_h,
+                                                 LoadW load_w) {
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
   constexpr int kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3;
   const T tf = (T)t, qf = (T)q;
 #pragma unroll
   for (int m = 0; m < E; ++m) {
     const int kx = t + TPF * m;
-    const size_t off = (size_t)kx * MH;
     Cx<T> h = v[m];
     if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) h = mk<T>((T)0, (T)0);
     if (m == 0) h = h + g0;  // g0 is zero except on row kx = 0 (t == 0)
     if (use_h) h = h + a.beta * load_h(m, kx);
-    stc(hmain + off, h);
+    store_h(m, kx, h);
     const T p = wave_p<T, P>(tf, m);
     const T lk = a.munu * (p * p + qf * qf);
     const Cx<T> wv = load_w(m, kx);
     w[m] = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
-    stc(wmain + off, w[m]);
+    store_w(m, kx, w[m]);
   }
 }
 
@@ -271,7 +271,9 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
     }
     Cx<T> g0 = mk<T>((T)0, (T)0);
     if (t == 0) g0 = ldc(G + q);
-    rk_update_column<T, P>(a, v, w, g0, use_h, t, q, hmain, wmain,
+    rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
+                           [&](int, int kx, Cx<T> h) { stc(hmain + (size_t)kx * MH, h); },
+                           [&](int, int kx, Cx<T> wn) { stc(wmain + (size_t)kx * MH, wn); },
                            [&](int, int kx) { return ldc(hmain + (size_t)kx * MH); },
                            [&](int, int kx) { return ldc(wmain + (size_t)kx * MH); });
   } else {
