@@ -18,6 +18,9 @@ SYMBOLS = (
     "kf_last_error", "kf_create", "kf_destroy", "kf_set_constants", "kf_rollout", "kf_rk_steps",
     "kf_reward_obs", "kf_step", "kf_step_host", "kf_profile_kernels", "kf_launch_count", "kf_workspace_bytes",
     "kf_chunk",
+    "kf_slab_create", "kf_slab_destroy", "kf_slab_set_constants", "kf_slab_set_action", "kf_slab_import",
+    "kf_slab_export", "kf_slab_exchange_bytes", "kf_slab_col", "kf_slab_row", "kf_slab_obs",
+    "kf_slab_launch_count", "kf_slab_workspace_bytes",
 )
 
 
@@ -66,6 +69,25 @@ def load():
     lib.kf_workspace_bytes.argtypes = [vp]
     lib.kf_workspace_bytes.restype = ctypes.c_size_t
     lib.kf_chunk.argtypes = [vp]
+    # slab-decomposed single grid
+    lib.kf_slab_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(KfConfig), ctypes.c_int, ctypes.c_int]
+    lib.kf_slab_destroy.argtypes = [vp]
+    lib.kf_slab_set_constants.argtypes = [vp, vp, vp]
+    lib.kf_slab_set_action.argtypes = [vp, vp, vp]
+    lib.kf_slab_import.argtypes = [vp, vp, vp]
+    lib.kf_slab_export.argtypes = [vp, vp, vp]
+    lib.kf_slab_exchange_bytes.argtypes = [vp, ctypes.c_int]
+    lib.kf_slab_exchange_bytes.restype = ctypes.c_size_t
+    lib.kf_slab_col.argtypes = [vp, ctypes.c_int, vp, vp, vp]
+    lib.kf_slab_row.argtypes = [vp, vp, vp, vp]
+    lib.kf_slab_obs.argtypes = [vp, vp, vp, vp, ctypes.c_double, vp]
+    for name in ("kf_slab_create", "kf_slab_destroy", "kf_slab_set_constants", "kf_slab_set_action",
+                 "kf_slab_import", "kf_slab_export", "kf_slab_col", "kf_slab_row", "kf_slab_obs"):
+        getattr(lib, name).restype = ctypes.c_int
+    lib.kf_slab_launch_count.argtypes = [vp]
+    lib.kf_slab_launch_count.restype = ctypes.c_longlong
+    lib.kf_slab_workspace_bytes.argtypes = [vp]
+    lib.kf_slab_workspace_bytes.restype = ctypes.c_size_t
     _lib = lib
     return lib
 

@@ -190,8 +190,8 @@ __device__ __forceinline__ void col_field_pair(const StageArgs<T>& a, LoadW load
 // RK accumulate + Crank-Nicolson update of one column (S:53-56, K:209-220): v[] holds the forward
 // x-transform of the advection column (column 0 already unpacked); load_h / load_w fetch the old
 // h / omega_hat of row kx, store_h / store_w dispose of the new ones.  Returns the new omega_hat in w[].
-template <typename T, class P, class StoreH, class StoreW, class LoadH, class LoadW>
-__device__ __forceinline__ void rk_update_column(const StageArgs<T>& a, const Cx<T>* v, Cx<T>* w, Cx<T> g0, bool use_h,
+template <typename T, class P, class Args, class StoreH, class StoreW, class LoadH, class LoadW>
+__device__ __forceinline__ void rk_update_column(const Args& a, const Cx<T>* v, Cx<T>* w, Cx<T> g0, bool use_h,
                                                  int t, int q, StoreH store_h, StoreW store_w, LoadH load_h,
                                                  LoadW load_w) {
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
@@ -300,25 +300,32 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
 // exchange.
 // ---------------------------------------------------------------------------
 
-// Z[k] = A[k] + i B[k] for the Hermitian extensions of the packed half-rows A, B (any lane type)
-template <typename X, class P>
-__device__ __forceinline__ void load_pair_hermitian(Cx<X>* z, const Cx<X>* __restrict__ A, const Cx<X>* __restrict__ B,
-                                                    int t) {
+// Z[k] = A[k] + i B[k] for the Hermitian extensions of the packed half-rows A, B (any lane type);
+// element k of a half-row lives at offset at(k) (identity for the batched layout, blocked for slabs)
+template <typename X, class P, class At>
+__device__ __forceinline__ void load_pair_hermitian_at(Cx<X>* z, const Cx<X>* __restrict__ A,
+                                                       const Cx<X>* __restrict__ B, int t, At at) {
   constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF;
 #pragma unroll
   for (int m = 0; m < E; ++m) {
     const int k = t + TPF * m;
     if (m < E / 2) {
-      const Cx<X> a = ldc(A + k), b = ldc(B + k);
+      const Cx<X> a = ldc(A + at(k)), b = ldc(B + at(k));
       const Cx<X> z0 = mk<X>(a.x, b.x), zk = mk<X>(a.x - b.y, a.y + b.x);
       z[m] = (k == 0) ? z0 : zk;
     } else {
       const int src = (k == MH) ? 0 : M - k;
-      const Cx<X> a = ldc(A + src), b = ldc(B + src);
+      const Cx<X> a = ldc(A + at(src)), b = ldc(B + at(src));
       const Cx<X> zh = mk<X>(a.y, b.y), zk = mk<X>(a.x + b.y, b.x - a.y);
       z[m] = (k == MH) ? zh : zk;
     }
   }
+}
+
+template <typename X, class P>
+__device__ __forceinline__ void load_pair_hermitian(Cx<X>* z, const Cx<X>* __restrict__ A, const Cx<X>* __restrict__ B,
+                                                    int t) {
+  load_pair_hermitian_at<X, P>(z, A, B, t, [](int k) { return k; });
 }
 
 template <typename T, int M> __host__ __device__ constexpr size_t row_exchange_elems() { return (size_t)M + M / 16; }

@@ -22,6 +22,13 @@ int fail(const std::string& msg) {
   return 1;
 }
 
+}  // namespace
+
+// shared with slab.cu
+int kf_set_error(const char* msg) { return fail(msg); }
+
+namespace {
+
 #define KF_CUDA(expr)                                                                     \
   do {                                                                                    \
     cudaError_t e__ = (expr);                                                             \

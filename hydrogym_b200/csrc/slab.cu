@@ -1,0 +1,382 @@
+// C-ABI of the slab-decomposed single-grid solver (include/kolmo_b200.h, kf_slab_*): per-rank workspace and
+// launch sequencing.  The cross-rank all-to-all between the two layouts is issued by the host between
+// kf_slab_col and kf_slab_row (torch.distributed / NCCL, hydrogym_b200/slab.py).  sm_100a only.
+#include "../../include/kolmo_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <string>
+#include <vector>
+
+#include "slab.cuh"
+
+int kf_set_error(const char* msg);  // kolmo_b200.cu: sets the thread-local message, returns 1
+
+namespace {
+
+int fail(const std::string& msg) { return kf_set_error(msg.c_str()); }
+
+#define KF_CUDA(expr)                                                                     \
+  do {                                                                                    \
+    cudaError_t e__ = (expr);                                                             \
+    if (e__ != cudaSuccess)                                                               \
+      return fail(std::string(#expr) + ": " + cudaGetErrorString(e__));                   \
+  } while (0)
+
+// reference coefficients, hydrogym/jax/solvers/base.py:13-15
+const double kAlpha[6] = {0, 0.1496590219993, 0.3704009573644, 0.6222557631345, 0.9582821306748, 1};
+const double kBeta[5] = {0, -0.4178904745, -1.192151694643, -1.697784692471, -1.514183444257};
+const double kGamma[5] = {0.1496590219993, 0.3792103129999, 0.8229550293869, 0.6994504559488, 0.1530572479681};
+
+struct SlabCtx;
+
+struct SlabOps {
+  size_t elem;  // bytes per complex
+  cudaError_t (*prepare)();
+  void (*col)(const SlabCtx&, int stage, const void* adv_recv, void* fld_send, cudaStream_t);
+  void (*row)(const SlabCtx&, const void* fld_recv, void* adv_send, cudaStream_t);
+  void (*obs)(const SlabCtx&, const void* fld_recv, double* acc, void* obs, double obs_w, cudaStream_t);
+  void (*import_)(const SlabCtx&, const void* user, cudaStream_t);
+  void (*export_)(const SlabCtx&, void* user, cudaStream_t);
+  void (*forcing)(const SlabCtx&, const void* action, cudaStream_t);
+};
+
+struct SlabCtx {
+  kf_config cfg;
+  const SlabOps* ops;
+  int N, MH, rank, P, Q, X, lgQ;
+  void *wk = nullptr, *hk = nullptr, *wnyq = nullptr, *hnyq = nullptr, *G = nullptr, *advk = nullptr, *fk = nullptr;
+  void *tw = nullptr, *F = nullptr, *C = nullptr;
+  size_t bytes = 0;
+  long long launches = 0;
+  bool have_constants = false;
+};
+
+template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
+  using C = kf::Cx<T>;
+  using C2 = kf::Cx<typename kf::PairOf<T>::type>;
+  static constexpr int N = P::L, MH = N / 2;
+  static size_t smem(int groups) { return sizeof(C) * (groups * kf::slab_exchange_elems<N>() + (size_t)N); }
+
+  static cudaError_t prepare() {
+    cudaError_t e;
+#define KF_ATTR(k, bytes)                                                                              \
+  e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes));              \
+  if (e != cudaSuccess) return e;
+    KF_ATTR((kf::slab_col_kernel<T, P, GROUPS, kf::kSlabStage, false, 1>), smem(GROUPS))
+    KF_ATTR((kf::slab_col_kernel<T, P, GROUPS, kf::kSlabInit, false, 1>), smem(GROUPS))
+    KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabStage, true, 1>), smem(1))
+    KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabInit, true, 1>), smem(1))
+    KF_ATTR((kf::slab_row_kernel<T, P, RGROUPS, 1>), smem(RGROUPS))
+    KF_ATTR((kf::slab_row_obs_kernel<T, P, RGROUPS>), smem(RGROUPS))
+#undef KF_ATTR
+    return cudaSuccess;
+  }
+
+  static kf::SlabArgs<T> args(const SlabCtx& c) {
+    kf::SlabArgs<T> a;
+    a.wk = (C*)c.wk; a.hk = (C*)c.hk; a.wnyq = (C*)c.wnyq; a.hnyq = (C*)c.hnyq;
+    a.G = (const C*)c.G; a.advk = (const C*)c.advk;
+    a.fak = (C2*)c.fk; a.fbk = a.fak + (size_t)c.Q * N;
+    a.fax = nullptr; a.fbx = nullptr; a.fblk = 2 * (size_t)c.X * c.Q; a.advx = nullptr;
+    a.tw = (const C*)c.tw;
+    a.beta = 0; a.gdt = 0; a.munu = 0;
+    a.scale = (T)(1.0 / ((double)N * (double)N));
+    a.dealias = c.cfg.dealias;
+    a.q0 = c.rank * c.Q; a.x0 = c.rank * c.X;
+    a.Q = c.Q; a.X = c.X; a.lgQ = c.lgQ;
+    return a;
+  }
+
+  template <typename V> static void transpose(const V* in, V* out, const kf::TransposeArgs& p, int nz, cudaStream_t s) {
+    const dim3 grid((p.Cn + 31) / 32, (p.R + 31) / 32, nz);
+    kf::transpose_kernel<V><<<grid, 256, 0, s>>>(in, out, p);
+  }
+
+  // stage >= 0: received advection blocks -> K layout -> sub-stage `stage` -> fields -> send blocks;
+  // stage < 0: fields of the stored omega_hat only
+  static void col(const SlabCtx& c, int stage, const void* adv_recv, void* fld_send, cudaStream_t s) {
+    kf::SlabArgs<T> a = args(c);
+    const int Q = c.Q, X = c.X;
+    if (stage >= 0) {
+      // adv_recv [P][X][Q] is [N][Q] with plain rows -> advk [Q][N]
+      kf::TransposeArgs p{N, Q, N, Q, 0, (size_t)Q, 0, 0, (size_t)N, 0};
+      transpose<C>((const C*)adv_recv, (C*)c.advk, p, 1, s);
+      a.beta = (T)kBeta[stage];
+      a.gdt = (T)(kGamma[stage] * c.cfg.dt);                                        // base.py:55
+      a.munu = (T)(0.5 * c.cfg.dt * (kAlpha[stage + 1] - kAlpha[stage]) * c.cfg.nu);  // base.py:54
+      if (c.rank == 0) kf::slab_col_kernel<T, P, 1, kf::kSlabStage, true, 1><<<1, P::TPF, smem(1), s>>>(a);
+      kf::slab_col_kernel<T, P, GROUPS, kf::kSlabStage, false, 1><<<Q / GROUPS, P::TPF * GROUPS, smem(GROUPS), s>>>(a);
+    } else {
+      if (c.rank == 0) kf::slab_col_kernel<T, P, 1, kf::kSlabInit, true, 1><<<1, P::TPF, smem(1), s>>>(a);
+      kf::slab_col_kernel<T, P, GROUPS, kf::kSlabInit, false, 1><<<Q / GROUPS, P::TPF * GROUPS, smem(GROUPS), s>>>(a);
+    }
+    // fak, fbk [Q][N] -> send [P][2][X][Q]: logical output row x at (x / X) * 2XQ + (x % X) * Q, array z at + z*XQ
+    kf::TransposeArgs p{Q, N, Q, X, 0, (size_t)N, (size_t)Q * N, 2 * (size_t)X * Q, (size_t)Q, (size_t)X * Q};
+    transpose<C2>((const C2*)c.fk, (C2*)fld_send, p, 2, s);
+  }
+
+  static void row(const SlabCtx& c, const void* fld_recv, void* adv_send, cudaStream_t s) {
+    kf::SlabArgs<T> a = args(c);
+    a.fax = (const C2*)fld_recv;
+    a.fbx = a.fax + (size_t)c.X * c.Q;
+    a.advx = (C*)adv_send;
+    kf::slab_row_kernel<T, P, RGROUPS, 1><<<c.X / 2 / RGROUPS, P::TPF * RGROUPS, smem(RGROUPS), s>>>(a);
+  }
+
+  static void obs(const SlabCtx& c, const void* fld_recv, double* acc, void* obs_dev, double obs_w, cudaStream_t s) {
+    kf::SlabArgs<T> a = args(c);
+    a.fax = (const C2*)fld_recv;
+    a.fbx = a.fax + (size_t)c.X * c.Q;
+    const int st = N / c.cfg.obs_size;
+    kf::slab_row_obs_kernel<T, P, RGROUPS><<<c.X / RGROUPS, P::TPF * RGROUPS, smem(RGROUPS), s>>>(
+        a, acc, (T*)obs_dev, c.cfg.obs_size, st, st, (T)obs_w);
+  }
+
+  // user omega_hat [N][M/2+1] (full array on every rank): this rank's columns <-> wk [Q][N], ky = M/2 <-> wnyq
+  static void import_(const SlabCtx& c, const void* user, cudaStream_t s) {
+    const C* u = (const C*)user;
+    kf::TransposeArgs p{N, c.Q, N, c.Q, 0, (size_t)(MH + 1), 0, 0, (size_t)N, 0};
+    transpose<C>(u + (size_t)c.rank * c.Q, (C*)c.wk, p, 1, s);
+    if (c.rank == 0) kf::strided_copy_kernel<C><<<(N + 255) / 256, 256, 0, s>>>(u + MH, MH + 1, (C*)c.wnyq, 1, N);
+  }
+  static void export_(const SlabCtx& c, void* user, cudaStream_t s) {
+    C* u = (C*)user;
+    kf::TransposeArgs p{c.Q, N, c.Q, N, 0, (size_t)N, 0, 0, (size_t)(MH + 1), 0};
+    transpose<C>((const C*)c.wk, u + (size_t)c.rank * c.Q, p, 1, s);
+    if (c.rank == 0) kf::strided_copy_kernel<C><<<(N + 255) / 256, 256, 0, s>>>((const C*)c.wnyq, 1, u + MH, MH + 1, N);
+  }
+  static void forcing(const SlabCtx& c, const void* action, cudaStream_t s) {
+    kf::forcing_row_kernel<T><<<dim3((MH + 1 + 127) / 128, 1), 128, 0, s>>>(
+        (C*)c.G, (const C*)c.F, (const C*)c.C, (const T*)action, (T)c.cfg.min_action, (T)c.cfg.max_action, MH + 1);
+  }
+
+  static SlabOps make() {
+    SlabOps o;
+    o.elem = sizeof(C);
+    o.prepare = prepare; o.col = col; o.row = row; o.obs = obs;
+    o.import_ = import_; o.export_ = export_; o.forcing = forcing;
+    return o;
+  }
+};
+
+const SlabOps* find_slab_ops(int dtype, int N) {
+  using kf::Plan;
+  static const SlabOps f256 = SlabImpl<float, Plan<256, 16, 16, 16>, 8, 8>::make();
+  static const SlabOps f1024 = SlabImpl<float, Plan<1024, 64, 16, 4, 16>, 2, 2>::make();
+  static const SlabOps f4096 = SlabImpl<float, Plan<4096, 256, 16, 16, 16>, 1, 1>::make();
+  static const SlabOps f8192 = SlabImpl<float, Plan<8192, 512, 16, 16, 2, 16>, 1, 1>::make();
+  static const SlabOps d256 = SlabImpl<double, Plan<256, 32, 8, 4, 8>, 4, 4>::make();
+  static const SlabOps d1024 = SlabImpl<double, Plan<1024, 128, 8, 2, 8, 8>, 1, 1>::make();
+  const bool f = dtype == KF_F32;
+  switch (N) {
+    case 256: return f ? &f256 : &d256;
+    case 1024: return f ? &f1024 : &d1024;
+    case 4096: return f ? &f4096 : nullptr;
+    case 8192: return f ? &f8192 : nullptr;
+    default: return nullptr;
+  }
+}
+
+int dev_alloc(SlabCtx& c, void** p, size_t bytes) {
+  KF_CUDA(cudaMalloc(p, bytes));
+  KF_CUDA(cudaMemset(*p, 0, bytes));
+  c.bytes += bytes;
+  return 0;
+}
+
+void free_all(SlabCtx& c) {
+  void* ptrs[] = {c.wk, c.hk, c.wnyq, c.hnyq, c.G, c.advk, c.fk, c.tw, c.F, c.C};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (prev >= 0 && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace
+
+struct kf_slab_s {
+  SlabCtx c;
+};
+
+extern "C" {
+
+int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks) {
+  if (!out || !cfg) return fail("kf_slab_create: null argument");
+  *out = nullptr;
+  if (cfg->N != cfg->M) return fail("kf_slab_create: only square grids are supported (N == M)");
+  if (cfg->dtype != KF_F32 && cfg->dtype != KF_F64) return fail("kf_slab_create: dtype must be KF_F32 or KF_F64");
+  const SlabOps* ops = find_slab_ops(cfg->dtype, cfg->N);
+  if (!ops) return fail("kf_slab_create: grid size must be 256 or 1024 (fp32, fp64), 4096 or 8192 (fp32)");
+  if (nranks < 1 || (nranks & (nranks - 1)) != 0) return fail("kf_slab_create: nranks must be a power of two");
+  if (rank < 0 || rank >= nranks) return fail("kf_slab_create: rank out of range");
+  if (cfg->N / 2 / nranks < 8) return fail("kf_slab_create: need at least 8 packed columns per rank");
+  if (cfg->drag != 0.0) return fail("kf_slab_create: drag must be 0 (the reference has no drag term)");
+  if (cfg->obs_size < 1 || cfg->N % cfg->obs_size != 0) return fail("kf_slab_create: obs_size must divide the grid size");
+  if (!(cfg->dt > 0.0) || !(cfg->nu >= 0.0)) return fail("kf_slab_create: need dt > 0 and nu >= 0");
+  int ndev = 0;
+  KF_CUDA(cudaGetDeviceCount(&ndev));
+  if (cfg->device < 0 || cfg->device >= ndev) return fail("kf_slab_create: no such CUDA device");
+  DeviceGuard guard(cfg->device);
+  cudaDeviceProp prop;
+  KF_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+  if (prop.major != 10) return fail("kf_slab_create: this library is built for sm_100a (B200) only");
+
+  kf_slab h = new kf_slab_s();
+  SlabCtx& c = h->c;
+  c.cfg = *cfg;
+  c.ops = ops;
+  c.N = cfg->N;
+  c.MH = cfg->N / 2;
+  c.rank = rank;
+  c.P = nranks;
+  c.Q = c.MH / nranks;
+  c.X = c.N / nranks;
+  c.lgQ = 0;
+  while ((1 << c.lgQ) < c.Q) ++c.lgQ;
+  const size_t el = ops->elem, qn = (size_t)c.Q * c.N;
+  int rc = 0;
+  cudaError_t pe = ops->prepare();
+  if (pe != cudaSuccess) rc = fail(std::string("kernel attribute setup: ") + cudaGetErrorString(pe));
+  if (!rc) rc = dev_alloc(c, &c.wk, el * qn);
+  if (!rc) rc = dev_alloc(c, &c.hk, el * qn);
+  if (!rc) rc = dev_alloc(c, &c.wnyq, el * c.N);
+  if (!rc) rc = dev_alloc(c, &c.hnyq, el * c.N);
+  if (!rc) rc = dev_alloc(c, &c.G, el * (c.MH + 1));
+  if (!rc) rc = dev_alloc(c, &c.advk, el * qn);
+  if (!rc) rc = dev_alloc(c, &c.fk, el * 4 * qn);
+  if (!rc) rc = dev_alloc(c, &c.tw, el * c.N);
+  if (!rc) rc = dev_alloc(c, &c.F, el * (c.MH + 1));
+  if (!rc) rc = dev_alloc(c, &c.C, el * 4 * (c.MH + 1));
+  if (!rc) {
+    std::vector<double> t64(2 * (size_t)c.N);
+    const double kPi = 3.14159265358979323846264338327950288;
+    for (int m = 0; m < c.N; ++m) {
+      t64[2 * m] = std::cos(2.0 * kPi * m / c.N);
+      t64[2 * m + 1] = -std::sin(2.0 * kPi * m / c.N);
+    }
+    cudaError_t e;
+    if (cfg->dtype == KF_F32) {
+      std::vector<float> t32(t64.begin(), t64.end());
+      e = cudaMemcpy(c.tw, t32.data(), el * c.N, cudaMemcpyHostToDevice);
+    } else {
+      e = cudaMemcpy(c.tw, t64.data(), el * c.N, cudaMemcpyHostToDevice);
+    }
+    if (e != cudaSuccess) rc = fail(std::string("twiddle upload: ") + cudaGetErrorString(e));
+  }
+  if (rc) {
+    free_all(c);
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return 0;
+}
+
+int kf_slab_destroy(kf_slab h) {
+  if (!h) return 0;
+  DeviceGuard guard(h->c.cfg.device);
+  cudaDeviceSynchronize();
+  free_all(h->c);
+  delete h;
+  return 0;
+}
+
+int kf_slab_set_constants(kf_slab h, const void* forcing_row, const void* control_rows) {
+  if (!h || !forcing_row || !control_rows) return fail("kf_slab_set_constants: null argument");
+  SlabCtx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  const size_t row = c.ops->elem * (c.MH + 1);
+  KF_CUDA(cudaMemcpy(c.F, forcing_row, row, cudaMemcpyHostToDevice));
+  KF_CUDA(cudaMemcpy(c.C, control_rows, 4 * row, cudaMemcpyHostToDevice));
+  c.have_constants = true;
+  return 0;
+}
+
+int kf_slab_set_action(kf_slab h, const void* action_dev, void* stream) {
+  if (!h) return fail("kf_slab_set_action: null handle");
+  SlabCtx& c = h->c;
+  if (!c.have_constants) return fail("kf_slab_set_constants has not been called");
+  DeviceGuard guard(c.cfg.device);
+  c.ops->forcing(c, action_dev, (cudaStream_t)stream);
+  c.launches += 1;
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int kf_slab_import(kf_slab h, const void* omega_hat_dev, void* stream) {
+  if (!h || !omega_hat_dev) return fail("kf_slab_import: null argument");
+  SlabCtx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  c.ops->import_(c, omega_hat_dev, (cudaStream_t)stream);
+  c.launches += c.rank == 0 ? 2 : 1;
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int kf_slab_export(kf_slab h, void* omega_hat_dev, void* stream) {
+  if (!h || !omega_hat_dev) return fail("kf_slab_export: null argument");
+  SlabCtx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  c.ops->export_(c, omega_hat_dev, (cudaStream_t)stream);
+  c.launches += c.rank == 0 ? 2 : 1;
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+size_t kf_slab_exchange_bytes(kf_slab h, int which) {
+  if (!h) return 0;
+  const SlabCtx& c = h->c;
+  const size_t tile = c.ops->elem * (size_t)c.N * c.Q;  // P blocks of [X][Q] complex
+  return which == 0 ? 4 * tile : tile;
+}
+
+int kf_slab_col(kf_slab h, int stage, const void* adv_recv_dev, void* fld_send_dev, void* stream) {
+  if (!h || !fld_send_dev) return fail("kf_slab_col: null argument");
+  if (stage > 4) return fail("kf_slab_col: stage must be 0..4, or negative for the fields of the stored state");
+  if (stage >= 0 && !adv_recv_dev) return fail("kf_slab_col: a sub-stage needs the received advection blocks");
+  SlabCtx& c = h->c;
+  if (stage >= 0 && !c.have_constants) return fail("kf_slab_set_constants has not been called");
+  DeviceGuard guard(c.cfg.device);
+  c.ops->col(c, stage, adv_recv_dev, fld_send_dev, (cudaStream_t)stream);
+  c.launches += (stage >= 0 ? 3 : 2) + (c.rank == 0 ? 1 : 0);
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int kf_slab_row(kf_slab h, const void* fld_recv_dev, void* adv_send_dev, void* stream) {
+  if (!h || !fld_recv_dev || !adv_send_dev) return fail("kf_slab_row: null argument");
+  SlabCtx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  c.ops->row(c, fld_recv_dev, adv_send_dev, (cudaStream_t)stream);
+  c.launches += 1;
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int kf_slab_obs(kf_slab h, const void* fld_recv_dev, double* acc4_dev, void* obs_dev, double obs_w, void* stream) {
+  if (!h || !fld_recv_dev || !acc4_dev) return fail("kf_slab_obs: null argument");
+  SlabCtx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  c.ops->obs(c, fld_recv_dev, acc4_dev, obs_dev, obs_w, (cudaStream_t)stream);
+  c.launches += 1;
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+long long kf_slab_launch_count(kf_slab h) { return h ? h->c.launches : 0; }
+size_t kf_slab_workspace_bytes(kf_slab h) { return h ? h->c.bytes : 0; }
+
+}  // extern "C"

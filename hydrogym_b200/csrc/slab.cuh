@@ -1,0 +1,347 @@
+// Slab-decomposed single-grid kernels (BASELINE.json configs[4]: one N x N Kolmogorov flow over P GPUs).
+//
+// The reference has no multi-device path for this solve; the arithmetic is the same RK sub-stage as
+// kernels.cuh (hydrogym/jax/solvers/base.py:50-57, hydrogym/jax/envs/kolmogorov.py:209-257), split at
+// the two places where a 2-D FFT changes direction:
+//
+//   K layout (rank r owns Q = M/2/P packed ky columns, ALL kx, kx contiguous: [Q][N]):
+//       slab_col_kernel : forward x-FFT of the advection columns -> forcing/control -> RK accumulate +
+//                         Crank-Nicolson update of h / omega_hat -> 4 spectral fields -> inverse x-FFT
+//   X layout (rank r owns X = N/P x rows, ALL ky, blocked by the peer that owns the columns: [P][X][Q]):
+//       slab_row_kernel : c2r y-FFT of the 4 fields -> -(gx*u + gy*v) -> r2c y-FFT
+//
+// Between them the data crosses ranks with an all-to-all whose blocks are exactly the [X][Q] tiles of the
+// blocked X layout; transpose_kernel turns K-layout rows into those tiles (and back) on the local GPU.
+// Column 0 of the packed x-space layout carries ky = 0 and ky = M/2 together (see kernels.cuh); it lives on
+// rank 0 and is handled by the SPECIAL instance of slab_col_kernel (one CTA).
+#pragma once
+#include "kernels.cuh"
+
+namespace kf {
+
+template <typename T> struct SlabArgs {
+  using L2 = typename PairOf<T>::type;
+  // K layout
+  Cx<T>* wk;            // [Q][N] omega_hat
+  Cx<T>* hk;            // [Q][N] RK register
+  Cx<T>* wnyq;          // [N] ky = M/2 column (rank 0)
+  Cx<T>* hnyq;          // [N]
+  const Cx<T>* G;       // [M/2+1] forcing + control row (kx = 0)
+  const Cx<T>* advk;    // [Q][N] packed x-space advection, transposed
+  Cx<L2>* fak;          // [Q][N] lanes (u_hat, gx_hat)
+  Cx<L2>* fbk;          // [Q][N] lanes (v_hat, gy_hat)
+  // X layout, blocked: element (xl, k) of a half-row at (k / Q) * blk + xl * Q + k % Q
+  const Cx<L2>* fax;    // fields received from the peers
+  const Cx<L2>* fbx;
+  size_t fblk;          // block stride of fax / fbx (2*X*Q: fa and fb of one peer are adjacent)
+  Cx<T>* advx;          // advection rows to send, block stride X*Q
+  const Cx<T>* tw;      // [N] exp(-2*pi*i*m/N)
+  T beta, gdt, munu, scale;
+  int dealias;
+  int q0;               // global packed-column index of local column 0 (rank * Q)
+  int x0;               // global x of local row 0 (rank * X)
+  int Q, X, lgQ;
+};
+
+// split exchange of one FFT group over a padded buffer of lane values (real parts, then imaginary parts)
+template <typename X, int TPF> struct RowExSplit {
+  static constexpr bool kSplit = true;
+  X* sm;
+  __device__ __forceinline__ static int pad(int pos) { return pos + (pos >> 4); }
+  __device__ __forceinline__ void store_part(int pos, X a) { stl(sm + pad(pos), a); }
+  __device__ __forceinline__ X load_part(int pos) { return ldl(sm + pad(pos)); }
+  __device__ __forceinline__ void sync() {
+    if (TPF <= 32) __syncwarp(); else __syncthreads();
+  }
+};
+
+template <int N> __host__ __device__ constexpr size_t slab_exchange_elems() { return (size_t)N + N / 16; }
+// per-CTA shared memory of the slab FFT kernels: one exchange buffer per group + the twiddle table
+template <typename T, int N, int GROUPS> __host__ __device__ constexpr size_t slab_smem_bytes() {
+  return sizeof(Cx<T>) * (GROUPS * slab_exchange_elems<N>() + (size_t)N);
+}
+
+enum SlabColMode { kSlabStage = 0, kSlabInit = 1 };
+
+// integer wavenumber of row index kx as a real
+template <typename T, int N> __device__ __forceinline__ T wave_of(int kx) { return (T)(kx < N / 2 ? kx : kx - N); }
+
+// ---------------------------------------------------------------------------
+// K-layout column kernel.  A group of TPF threads owns local column ql (a contiguous run of N kx values);
+// thread t holds rows {t + TPF*m}.  grid = Q / GROUPS (normal) or 1 CTA with GROUPS = 1 (SPECIAL, rank 0,
+// packed column 0 = ky 0 and ky M/2).  The normal instance computes global column 0 too but discards it.
+// ---------------------------------------------------------------------------
+template <typename T, class P, int GROUPS, int MODE, bool SPECIAL, int MINB>
+__global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs<T> a) {
+  using L2 = typename PairOf<T>::type;
+  constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
+  constexpr size_t EXN = slab_exchange_elems<N>();
+  static_assert(sizeof(Cx<T>) == sizeof(L2), "scalar-complex and lane-pair exchange buffers coincide");
+  static_assert(!SPECIAL || GROUPS == 1, "the packed column is one CTA");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
+  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<T>);
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<T>));
+  RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
+  RowExSplit<L2, TPF> ex2{reinterpret_cast<L2*>(s_g)};
+  const int ql = SPECIAL ? 0 : blockIdx.x * GROUPS + g;
+  const int q = a.q0 + ql;
+  const bool live = SPECIAL || q != 0;
+  const T tf = (T)t, qf = (T)q;
+  Cx<T>* wrow = a.wk + (size_t)ql * N;
+  Cx<T>* hrow = a.hk + (size_t)ql * N;
+
+  for (int i = threadIdx.x; i < N; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
+  __syncthreads();
+
+  Cx<T> w[E];
+  Cx<T> wn[SPECIAL ? E : 1];  // ky = M/2 column (SPECIAL only)
+  if constexpr (MODE == kSlabStage) {
+    const bool use_h = (a.beta != (T)0);
+    Cx<T> v[E];
+    const Cx<T>* arow = a.advk + (size_t)ql * N;
+#pragma unroll
+    for (int m = 0; m < E; ++m) v[m] = ldc(arow + t + TPF * m);
+    fft_regs<P, -1, T>(v, s_tw, t, ex1);
+    if constexpr (SPECIAL) {
+      // unpack: A0[kx] = (W[kx] + conj(W[-kx]))/2 (ky = 0), An[kx] = (W[kx] - conj(W[-kx]))/(2i) (ky = M/2)
+#pragma unroll
+      for (int m = 0; m < E; ++m) ex1.store(t + TPF * m, v[m]);
+      __syncthreads();
+#pragma unroll
+      for (int m = 0; m < E; ++m) {
+        const int kx = t + TPF * m;
+        const Cx<T> wm = ex1.load((N - kx) & (N - 1));
+        const Cx<T> d = v[m] - conj(wm);
+        v[m] = (T)0.5 * add_conj(v[m], wm);
+        Cx<T> h = mk<T>((T)0.5 * d.y, (T)-0.5 * d.x);
+        if (a.dealias) h = mk<T>((T)0, (T)0);  // ky = M/2 >= km always
+        if (kx == 0) h = h + ldc(a.G + MH);
+        if (use_h) h = h + a.beta * ldc(a.hnyq + kx);
+        stc(a.hnyq + kx, h);
+        const T p = wave_of<T, N>(kx);
+        const T lk = a.munu * (p * p + (T)MH * (T)MH);
+        const Cx<T> wv = ldc(a.wnyq + kx);
+        wn[m] = fast_rcp((T)1 + lk) * (wv + a.gdt * h - lk * wv);
+        stc(a.wnyq + kx, wn[m]);
+      }
+      __syncthreads();
+    }
+    Cx<T> g0 = mk<T>((T)0, (T)0);
+    if (t == 0) g0 = ldc(a.G + q);
+    rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
+                           [&](int, int kx, Cx<T> h) { if (live) stc(hrow + kx, h); },
+                           [&](int, int kx, Cx<T> wv) { if (live) stc(wrow + kx, wv); },
+                           [&](int, int kx) { return ldc(hrow + kx); },
+                           [&](int, int kx) { return ldc(wrow + kx); });
+  } else {
+#pragma unroll
+    for (int m = 0; m < E; ++m) w[m] = ldc(wrow + t + TPF * m);
+    if constexpr (SPECIAL) {
+#pragma unroll
+      for (int m = 0; m < E; ++m) wn[m] = ldc(a.wnyq + t + TPF * m);
+    }
+  }
+
+  // mirrored omega_hat values of the packed column, read back from global memory (this CTA wrote them)
+  Cx<T> w0m[SPECIAL ? E : 1], wnm[SPECIAL ? E : 1];
+  if constexpr (SPECIAL) {
+    __syncthreads();
+#pragma unroll
+    for (int m = 0; m < E; ++m) {
+      const int mkx = (N - (t + TPF * m)) & (N - 1);
+      w0m[m] = ldc(wrow + mkx);
+      wnm[m] = ldc(a.wnyq + mkx);
+    }
+  }
+
+#pragma unroll
+  for (int pair = 0; pair < 2; ++pair) {
+    Cx<L2> f[E];
+#pragma unroll
+    for (int m = 0; m < E; ++m) {
+      const T p = wave_p<T, P>(tf, m);
+      const L2 cf = pair == 0 ? pair_coef<0, T>(p, qf, a.scale) : pair_coef<1, T>(p, qf, a.scale);
+      f[m] = coef_times_iw<T>(cf, w[m]);
+      if constexpr (SPECIAL) {
+        // column 0 <- herm(field[:,0]) + i*herm(field[:,M/2]); herm(c)[kx] = (c[kx] + conj(c[-kx]))/2
+        const int mkx = (N - (t + TPF * m)) & (N - 1);
+        const T pm = wave_of<T, N>(mkx);
+        const L2 cfm = pair == 0 ? pair_coef<0, T>(pm, (T)0, a.scale) : pair_coef<1, T>(pm, (T)0, a.scale);
+        const L2 cn = pair == 0 ? pair_coef<0, T>(p, (T)MH, a.scale) : pair_coef<1, T>(p, (T)MH, a.scale);
+        const L2 cnm = pair == 0 ? pair_coef<0, T>(pm, (T)MH, a.scale) : pair_coef<1, T>(pm, (T)MH, a.scale);
+        const Cx<L2> ah = add_conj(f[m], coef_times_iw<T>(cfm, w0m[m]));
+        const Cx<L2> bh = add_conj(coef_times_iw<T>(cn, wn[m]), coef_times_iw<T>(cnm, wnm[m]));
+        f[m] = mk<L2>((ah.x - bh.y) * L2(0.5), (ah.y + bh.x) * L2(0.5));
+      }
+    }
+    fft_regs<P, +1, L2>(f, s_tw, t, ex2);
+    Cx<L2>* out = (pair == 0 ? a.fak : a.fbk) + (size_t)ql * N;
+    if (live) {
+#pragma unroll
+      for (int m = 0; m < E; ++m) stc(out + t + TPF * m, f[m]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// X-layout row kernel: the arithmetic of row_kernel (kernels.cuh) on the blocked slab layout.  A group of
+// TPF threads owns the local rows (xl0, xl0 + 1); grid = X / 2 / GROUPS.
+// ---------------------------------------------------------------------------
+template <typename T, class P, int GROUPS, int MINB>
+__global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_row_kernel(SlabArgs<T> a) {
+  using L2 = typename PairOf<T>::type;
+  constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF;
+  constexpr size_t EXN = slab_exchange_elems<M>();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
+  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<T>);
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<T>));
+  RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
+  RowExSplit<L2, TPF> ex2{reinterpret_cast<L2*>(s_g)};
+  const int xl0 = 2 * (blockIdx.x * GROUPS + g);
+  const int Q = a.Q, lgQ = a.lgQ;
+
+  for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
+  __syncthreads();
+
+  Cx<T> v[E];
+#pragma unroll
+  for (int rr = 0; rr < 2; ++rr) {
+    const size_t roff = (size_t)(xl0 + rr) * Q;
+    const size_t blk = a.fblk;
+    Cx<L2> z[E];
+    load_pair_hermitian_at<L2, P>(z, a.fax + roff, a.fbx + roff, t,
+                                  [&](int k) { return (size_t)(k >> lgQ) * blk + (k & (Q - 1)); });
+    fft_regs<P, +1, L2>(z, s_tw, t, ex2);
+#pragma unroll
+    for (int m = 0; m < E; ++m) {
+      const T adv = -(z[m].x.lo() * z[m].x.hi() + z[m].y.lo() * z[m].y.hi());  // kolmogorov.py:249
+      if (rr == 0) v[m].x = adv; else v[m].y = adv;
+    }
+  }
+
+  fft_regs<P, -1, T>(v, s_tw, t, ex1);
+#pragma unroll
+  for (int m = 0; m < E; ++m) ex1.store(t + TPF * m, v[m]);
+  ex1.sync();
+  const size_t ablk = (size_t)a.X * Q;
+  Cx<T>* o0 = a.advx + (size_t)xl0 * Q;
+  Cx<T>* o1 = o0 + Q;
+#pragma unroll
+  for (int m = 0; m < E / 2; ++m) {
+    const int k = t + TPF * m;
+    const size_t off = (size_t)(k >> lgQ) * ablk + (k & (Q - 1));
+    if (k == 0) {
+      const Cx<T> wn = ex1.load(MH);
+      stc(o0, mk<T>(v[m].x, wn.x));
+      stc(o1, mk<T>(v[m].y, wn.y));
+    } else {
+      const Cx<T> wm = ex1.load(M - k);
+      const Cx<T> s = add_conj(v[m], wm), d = sub_conj(v[m], wm);
+      stc(o0 + off, (T)0.5 * s);
+      stc(o1 + off, mk<T>((T)0.5 * d.y, (T)-0.5 * d.x));
+    }
+  }
+}
+
+// Reward / observation partial sums of this rank's rows (compute_tke utils.py:175-194,
+// _trajectory_mean_obs kolmogorov.py:426-446): acc[4] += (sum u, sum v, sum u^2, sum v^2) over the local
+// rows; |velocity| at the probes that fall on local rows is added to obs with weight obs_w.  The host sums
+// acc and obs over the ranks.  One row per group; grid = X / GROUPS.
+template <typename T, class P, int GROUPS>
+__global__ void __launch_bounds__(P::TPF* GROUPS) slab_row_obs_kernel(SlabArgs<T> a, double* acc, T* obs, int nobs,
+                                                                      int sx, int sy, T obs_w) {
+  using L2 = typename PairOf<T>::type;
+  constexpr int M = P::L, E = P::E, TPF = P::TPF;
+  constexpr size_t EXN = slab_exchange_elems<M>();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
+  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<T>);
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<T>));
+  RowExSplit<L2, TPF> ex2{reinterpret_cast<L2*>(s_g)};
+  const int xl = blockIdx.x * GROUPS + g;
+  const int x = a.x0 + xl;
+  const int Q = a.Q, lgQ = a.lgQ;
+
+  for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
+  __syncthreads();
+
+  const size_t roff = (size_t)xl * Q, blk = a.fblk;
+  Cx<L2> z[E];
+  load_pair_hermitian_at<L2, P>(z, a.fax + roff, a.fbx + roff, t,
+                                [&](int k) { return (size_t)(k >> lgQ) * blk + (k & (Q - 1)); });
+  fft_regs<P, +1, L2>(z, s_tw, t, ex2);
+
+  T su = 0, sv = 0, suu = 0, svv = 0;
+#pragma unroll
+  for (int m = 0; m < E; ++m) {
+    const T u = z[m].x.lo(), vv = z[m].y.lo();
+    su += u; sv += vv;
+    suu += u * u; svv += vv * vv;
+  }
+  if (obs && x % sx == 0 && x / sx < nobs) {
+#pragma unroll
+    for (int m = 0; m < E; ++m) {
+      const int y = t + TPF * m;
+      if (y % sy == 0 && y / sy < nobs) {
+        const T u = z[m].x.lo(), vv = z[m].y.lo();
+        obs[(x / sx) * nobs + y / sy] += obs_w * sqrt(u * u + vv * vv);  // single writer per launch
+      }
+    }
+  }
+  double r[4] = {(double)su, (double)sv, (double)suu, (double)svv};
+  // threads of a warp may belong to different rows of the same slab: all of them add into the same sums
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r[i] += __shfl_xor_sync(0xffffffffu, r[i], off);
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) atomicAdd(acc + i, r[i]);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Tiled transpose with blocked row addressing on both sides: logical in[R][Cn] -> out[Cn][R], where
+// logical input row r starts at (r / in_rpb) * in_blk + (r % in_rpb) * in_ld and logical output row c at
+// (c / out_rpb) * out_blk + (c % out_rpb) * out_ld.  blockIdx.z selects one of several arrays
+// (in + z * in_z, out + z * out_z).  V is any 8 / 16 / 32-byte element.
+// ---------------------------------------------------------------------------
+struct TransposeArgs {
+  int R, Cn;
+  int in_rpb, out_rpb;
+  size_t in_blk, in_ld, in_z;
+  size_t out_blk, out_ld, out_z;
+};
+
+template <typename V> __global__ void __launch_bounds__(256) transpose_kernel(const V* __restrict__ in, V* __restrict__ out,
+                                                                              TransposeArgs p) {
+  __shared__ V tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  in += (size_t)blockIdx.z * p.in_z;
+  out += (size_t)blockIdx.z * p.out_z;
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int r = r0 + ty + i, c = c0 + tx;
+    if (r < p.R && c < p.Cn) tile[ty + i][tx] = in[(size_t)(r / p.in_rpb) * p.in_blk + (size_t)(r % p.in_rpb) * p.in_ld + c];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int c = c0 + ty + i, r = r0 + tx;
+    if (r < p.R && c < p.Cn)
+      out[(size_t)(c / p.out_rpb) * p.out_blk + (size_t)(c % p.out_rpb) * p.out_ld + r] = tile[tx][ty + i];
+  }
+}
+
+// strided column copy: dst[i * dst_ld] = src[i * src_ld], i < n (the ky = M/2 column of the user layout)
+template <typename V> __global__ void strided_copy_kernel(const V* __restrict__ src, size_t src_ld, V* __restrict__ dst,
+                                                          size_t dst_ld, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[(size_t)i * dst_ld] = src[(size_t)i * src_ld];
+}
+
+}  // namespace kf

@@ -94,6 +94,46 @@ size_t kf_workspace_bytes(kf_handle h);
 /* Environments per chunk actually used. */
 int kf_chunk(kf_handle h);
 
+/* ---------------------------------------------------------------------------------------------
+ * Slab-decomposed single grid (BASELINE.json configs[4]: one N x N flow over P GPUs, one process per
+ * GPU).  The reference has no multi-device path; the arithmetic is the same RK sub-stage
+ * (hydrogym/jax/solvers/base.py:50-57, hydrogym/jax/envs/kolmogorov.py:209-257).  Rank r owns, in
+ * spectral space, Q = M/2/P packed ky columns of omega_hat and of the RK register (all kx), and in
+ * x-space X = N/P rows (all ky).  One sub-stage is
+ *     kf_slab_row(fld_recv -> adv_send);  all-to-all(adv_send -> adv_recv);
+ *     kf_slab_col(stage, adv_recv -> fld_send);  all-to-all(fld_send -> fld_recv);
+ * the host issues the two all-to-alls (NCCL through torch.distributed, equal splits: block d of a send
+ * buffer goes to rank d, block s of a recv buffer comes from rank s).  Exchange buffers are caller-owned
+ * device memory of kf_slab_exchange_bytes(h, 0) (fields) / (h, 1) (advection) bytes each.  With P = 1 the
+ * all-to-all is the identity (send and recv may be the same buffer).
+ * cfg->B, n_inner, n_outer, chunk and use_graph are ignored.  Grid sizes: 256, 1024 (fp32, fp64),
+ * 4096, 8192 (fp32).
+ */
+typedef struct kf_slab_s* kf_slab;
+
+int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks);
+int kf_slab_destroy(kf_slab h);
+/* Same host arrays as kf_set_constants (every rank needs row kx = 0 of its own columns only, but takes all). */
+int kf_slab_set_constants(kf_slab h, const void* forcing_row, const void* control_rows);
+/* G = F + sum_m clip(a_m) C_m for action_dev[4] real (NULL = no control). */
+int kf_slab_set_action(kf_slab h, const void* action_dev, void* stream);
+/* omega_hat_dev: the FULL user-layout state [N][M/2+1] complex on this device; import reads this rank's
+ * columns, export writes this rank's columns (and leaves the others untouched). */
+int kf_slab_import(kf_slab h, const void* omega_hat_dev, void* stream);
+int kf_slab_export(kf_slab h, void* omega_hat_dev, void* stream);
+size_t kf_slab_exchange_bytes(kf_slab h, int which);
+/* stage 0..4: RK sub-stage on this rank's columns; stage < 0: only the x-space fields of the stored
+ * omega_hat (start of a run / observation), adv_recv_dev may then be NULL. */
+int kf_slab_col(kf_slab h, int stage, const void* adv_recv_dev, void* fld_send_dev, void* stream);
+int kf_slab_row(kf_slab h, const void* fld_recv_dev, void* adv_send_dev, void* stream);
+/* Partial reward / observation sums of this rank's rows from the received fields of a snapshot:
+ * acc4_dev[4] += (sum u, sum v, sum u^2, sum v^2) (fp64); obs_dev[obs_size^2] (real, may be NULL) +=
+ * obs_w * |velocity| at the probes on this rank's rows.  The host sums both over the ranks
+ * (compute_tke utils.py:175-194, _trajectory_mean_obs kolmogorov.py:426-446). */
+int kf_slab_obs(kf_slab h, const void* fld_recv_dev, double* acc4_dev, void* obs_dev, double obs_w, void* stream);
+long long kf_slab_launch_count(kf_slab h);
+size_t kf_slab_workspace_bytes(kf_slab h);
+
 #ifdef __cplusplus
 }
 #endif

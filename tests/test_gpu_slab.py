@@ -1,0 +1,120 @@
+"""GPU parity of the slab-decomposed single-grid solver (kf_slab_*): against the NumPy oracle, against the
+batched kernels, and across decompositions.  ``local_ranks=P`` plays P ranks on one device with the same
+kernels and layouts as the NCCL driver (tests/test_gpu_slab_nccl.py covers the collective itself)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import kolmogorov_oracle as orc
+from test_gpu_parity import ACTION, random_states, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def make_slab(N, Re, dtype, P, **kw):
+    from hydrogym_b200.slab import SlabKolmogorovSolver
+    return SlabKolmogorovSolver(grid_size=(N, N), Re=Re, dtype=dtype, device="cuda:0", local_ranks=P, **kw)
+
+
+@pytest.mark.parametrize("P", [1, 2, 4, 8])
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-11), (torch.float32, 2e-5)])
+def test_slab_256_matches_oracle(P, dtype, tol):
+    N, steps = 256, 3
+    npdt = np.float64 if dtype == torch.float64 else np.float32
+    ref = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=npdt)
+    w0 = random_states(ref, 1, seed=11).astype(orc._ctype(npdt))
+    action = np.array([0.7, -0.3, 0.1, -0.6], dtype=npdt)  # first one outside the clip range
+    clipped = ref._clip_action(action[None], ref.default_params)
+    ch = ref.equation.control_term(w0, ref._control_field(clipped, ref.default_params))
+    want = ref.integrator.rk_steps(w0.copy(), steps, ch)[0]
+    sl = make_slab(N, 100, dtype, P)
+    sl.set_state(torch.from_numpy(w0[0]).cuda(), torch.from_numpy(action).cuda())
+    sl.rk_steps(steps)
+    got = sl.get_state().cpu().numpy()
+    sl.close()
+    assert np.isfinite(got).all()
+    assert rel_l2(got, want) < tol, rel_l2(got, want)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-11), (torch.float32, 2e-5)])
+def test_slab_1024_matches_batched_kernels(dtype, tol):
+    from hydrogym_b200 import KolmogorovStepper
+    N, steps = 1024, 2
+    npdt = np.float64 if dtype == torch.float64 else np.float32
+    ref = orc.KolmogorovFlow(flow_config=dict(Re=1000, grid_size=(N, N)), dtype=npdt)
+    w0 = random_states(ref, 1, seed=5).astype(orc._ctype(npdt))
+    act = torch.tensor(ACTION, dtype=dtype, device="cuda")
+    st = KolmogorovStepper(grid_size=(N, N), Re=1000, num_envs=1, dtype=dtype, device="cuda:0")
+    w = torch.from_numpy(w0).cuda()
+    st.rk_steps(w, act[None], steps)
+    want = w[0].cpu().numpy()
+    st.close()
+    for P in (1, 4):
+        sl = make_slab(N, 1000, dtype, P)
+        sl.set_state(torch.from_numpy(w0[0]).cuda(), act)
+        sl.rk_steps(steps)
+        got = sl.get_state().cpu().numpy()
+        sl.close()
+        assert rel_l2(got, want) < tol, (P, rel_l2(got, want))
+
+
+@pytest.mark.parametrize("P", [1, 4])
+def test_slab_reward_obs_matches_oracle(P):
+    N = 256
+    ref = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=np.float64)
+    w0 = random_states(ref, 1, seed=2).astype(np.complex128)[0]
+    sl = make_slab(N, 100, torch.float64, P)
+    sl.set_state(torch.from_numpy(w0).cuda(), None)
+    obs, tke = sl.reward_obs()
+    sl.close()
+    want_obs = ref._trajectory_mean_obs(w0[None])
+    want_tke = ref._avg_tke(w0[None])
+    assert np.abs(obs.cpu().numpy() - want_obs).max() < 1e-10
+    assert abs(float(tke) - float(want_tke)) < 1e-10 * max(1.0, abs(float(want_tke)))
+
+
+def _band_limited(N, K, seed, dtype):
+    """Hermitian-consistent random state with |kx|, ky <= K on an N x N grid, as omega_hat of rfft2 scaling."""
+    rng = np.random.default_rng(seed)
+    w = np.zeros((N, N // 2 + 1), dtype=np.complex128)
+    kx = np.r_[0:K + 1, N - K:N]
+    blk = rng.normal(size=(len(kx), K + 1)) + 1j * rng.normal(size=(len(kx), K + 1))
+    w[np.ix_(kx, np.arange(K + 1))] = blk
+    w = np.fft.rfft2(np.fft.irfft2(w, s=(N, N)))  # make it the transform of a real field
+    w[0, 0] = 0
+    return (w * (N * N) * 0.2).astype(dtype)
+
+
+def test_slab_8192_band_limited_matches_1024():
+    """No oracle runs at 8192^2 in seconds.  A state band-limited to K = 8 stays alias-free through one RK
+    step (five products: 32 K = 256 < 512) on BOTH a 1024^2 and an 8192^2 grid, so the two grids must give
+    the same spectrum up to the (N^2) transform scaling.  Forcing / control rows are zeroed (they are
+    grid-dependent by the reference's endpoint-inclusive sampling)."""
+    from hydrogym_b200 import KolmogorovStepper
+    K, Ns, Nl = 8, 1024, 8192
+    ws = _band_limited(Ns, K, 3, np.complex64)
+    wl = np.zeros((Nl, Nl // 2 + 1), dtype=np.complex64)
+    kxs = np.r_[0:K + 1, Ns - K:Ns]
+    kxl = np.r_[0:K + 1, Nl - K:Nl]
+    wl[np.ix_(kxl, np.arange(K + 1))] = ws[np.ix_(kxs, np.arange(K + 1))] * (Nl / Ns) ** 2
+    st = KolmogorovStepper(grid_size=(Ns, Ns), Re=1000, num_envs=1, dtype=torch.float32, device="cuda:0")
+    st.forcing_row[:] = 0
+    st.set_control_rows(np.zeros_like(st.control_rows))
+    w = torch.from_numpy(ws[None]).cuda()
+    st.rk_steps(w, None, 1)
+    want = w[0].cpu().numpy()
+    st.close()
+    for P in (1, 8):
+        sl = make_slab(Nl, 1000, torch.float32, P, zero_forcing=True)
+        sl.set_state(torch.from_numpy(wl).cuda(), None)
+        sl.rk_steps(1)
+        got = sl.get_state().cpu().numpy()
+        sl.close()
+        kk = 32 * K
+        a = got[np.ix_(np.r_[0:kk + 1, Nl - kk:Nl], np.arange(kk + 1))] / (Nl / Ns) ** 2
+        b = want[np.ix_(np.r_[0:kk + 1, Ns - kk:Ns], np.arange(kk + 1))]
+        assert rel_l2(a, b) < 5e-5, (P, rel_l2(a, b))
+        # nothing outside the band
+        mask = np.ones(got.shape, dtype=bool)
+        mask[np.ix_(np.r_[0:kk + 1, Nl - kk:Nl], np.arange(kk + 1))] = False
+        assert np.abs(got[mask]).max() < 1e-4 * np.abs(a).max() * (Nl / Ns) ** 2
