@@ -76,11 +76,12 @@ template <typename T, class P, int TC, int STAGES> struct ColTmaSmem {
   static constexpr size_t bytes() { return 3 * STAGES * kTile + 2 * (size_t)N * sizeof(Cx<T>) + 64; }
 };
 
-template <typename T, class P, int TC, int MINB, int STAGES>
+template <typename T, class P, int TC, int MINB, int STAGES, bool TSTORE = (STAGES == 2)>
 __global__ void __launch_bounds__(P::TPF* TC, MINB)
     col_tma_kernel(StageArgs<T> a, const __grid_constant__ CUtensorMap m_adv, const __grid_constant__ CUtensorMap m_h,
                    const __grid_constant__ CUtensorMap m_w, int ntiles) {
   static_assert(STAGES == 1 || STAGES == 2, "one or two input stages");
+  static_assert(!TSTORE || STAGES == 2, "TMA stores reuse the advection buffer of a two-stage ring");
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2, TILES = MH / TC;
   constexpr int RB = N < 256 ? N : 256, NBOX = N / RB;  // TMA box rows (<= 256)
   constexpr uint32_t kBytes = (uint32_t)((size_t)N * TC * sizeof(Cx<T>));
@@ -184,7 +185,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     mbar_wait(bar + 2, par);
     {
       Cx<T> w[E];
-      if constexpr (STAGES == 2) {
+      if constexpr (TSTORE) {
         // new h -> buf_adv, new omega_hat -> buf_w (in place); both tiles leave through TMA stores
         rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
                                [&](int, int kx, Cx<T> h) { stc(buf_adv + kx * TC + c, h); },
@@ -218,16 +219,14 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     col_field_pair<1, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
     __syncthreads();  // every thread has read its omega_hat for the second pair and left the last exchange
     if (tid == 0 && has_next) {
-      if (STAGES == 2) {
-        bulk_wait_read0();  // the TMA stores have read buf_adv / buf_w
-        issue(buf_adv, &m_adv, bar + 0, next);
-      }
+      if (TSTORE) bulk_wait_read0();  // the TMA stores have read buf_adv / buf_w
       fence_proxy_async();
+      if (STAGES == 2) issue(buf_adv, &m_adv, bar + 0, next);
       if (use_h) issue(buf_h, &m_h, bar + 1, next);
       issue(buf_w, &m_w, bar + 2, next);
     }
   }
-  if (STAGES == 2 && tid == 0) bulk_wait0();  // all TMA stores have landed before the CTA retires
+  if (TSTORE && tid == 0) bulk_wait0();  // all TMA stores have landed before the CTA retires
 }
 
 }  // namespace kf

@@ -94,7 +94,7 @@ struct Ctx {
 
 // TC: columns per column-kernel CTA; GROUPS: FFT groups per row-kernel CTA;
 // CB / RB: __launch_bounds__ min-blocks (register caps) of the column / row kernels.
-template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int TB = 1, int ST = 1> struct Impl {
+template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int TB = 1, int ST = 1, bool TS = false> struct Impl {
   using C = kf::Cx<T>;
   static constexpr int N = P::L, MH = N / 2;
   using C2 = kf::Cx<typename kf::PairOf<T>::type>;  // lane-paired complex (two transforms per element)
@@ -167,7 +167,7 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     a.beta = (T)st.beta; a.gdt = (T)st.gdt; a.munu = (T)st.munu;
     const int ntiles = nb * (MH / TC);
     const int grid = ntiles < c.tma_ctas ? ntiles : c.tma_ctas;
-    kf::col_tma_kernel<T, P, TC, TB, ST><<<grid, P::TPF * TC, kf::ColTmaSmem<T, P, TC, ST>::bytes(), s>>>(
+    kf::col_tma_kernel<T, P, TC, TB, ST, TS><<<grid, P::TPF * TC, kf::ColTmaSmem<T, P, TC, ST>::bytes(), s>>>(
         a, c.tm_adv, c.tm_h, c.tm_w, ntiles);
   }
   static Ops make() {
@@ -199,12 +199,12 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-template <typename T, class P, int TC, int GROUPS, int CB, int RB, int TB, int ST>
-int Impl<T, P, TC, GROUPS, CB, RB, TB, ST>::tma_setup(Ctx& c) {
+template <typename T, class P, int TC, int GROUPS, int CB, int RB, int TB, int ST, bool TS>
+int Impl<T, P, TC, GROUPS, CB, RB, TB, ST, TS>::tma_setup(Ctx& c) {
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) return fail("cuTensorMapEncodeTiled is not available from this driver");
   const size_t smem = kf::ColTmaSmem<T, P, TC, ST>::bytes();
-  auto kern = kf::col_tma_kernel<T, P, TC, TB, ST>;
+  auto kern = kf::col_tma_kernel<T, P, TC, TB, ST, TS>;
   KF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0, sms = 0;
   KF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, P::TPF * TC, smem));
@@ -248,7 +248,10 @@ int Impl<T, P, TC, GROUPS, CB, RB, TB, ST>::tma_setup(Ctx& c) {
 #ifndef KF_F256_ST
 #define KF_F256_ST 1
 #endif
-#define KF_CFG_F256 KF_F256_TC, KF_F256_GROUPS, KF_F256_CB, KF_F256_RB, KF_F256_TB, KF_F256_ST
+#ifndef KF_F256_TS
+#define KF_F256_TS false
+#endif
+#define KF_CFG_F256 KF_F256_TC, KF_F256_GROUPS, KF_F256_CB, KF_F256_RB, KF_F256_TB, KF_F256_ST, KF_F256_TS
 #define KF_CFG_D256 8, 4, 2, 4, 2
 #define KF_CFG_F128 16, 16
 

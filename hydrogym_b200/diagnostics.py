@@ -1,0 +1,57 @@
+"""Spectral diagnostics on device: CUDA reductions behind ``kf_energy_spectrum`` plus the
+per-mode helpers of hydrogym/jax/utils/utils.py:89-126 as thin indexing ops over torch tensors."""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+
+
+def energy_spectrum(omega_hat: torch.Tensor, nbins: int | None = None) -> torch.Tensor:
+    """Radial kinetic-energy spectrum E[b, k] (float64) of ``omega_hat`` (B, N, N//2+1) or (N, N//2+1).
+
+    Per-mode energy as in ``compute_energy_mode`` (utils.py:89-101): 0.5 (|u_hat|^2 + |v_hat|^2) / (n m)^2 with
+    the velocities of ``compute_velocity_fft`` (utils.py:53-69); bin = round(|k|); the conjugate half-plane is
+    counted by weights 2 on 0 < ky < N/2.
+    """
+    squeeze = omega_hat.dim() == 2
+    w = omega_hat[None] if squeeze else omega_hat
+    if w.dim() != 3 or w.shape[2] != w.shape[1] // 2 + 1:
+        raise ValueError("omega_hat must be (B, N, N//2+1) complex")
+    if w.dtype not in (torch.complex64, torch.complex128) or not w.is_cuda:
+        raise ValueError("omega_hat must be a complex CUDA tensor")
+    w = w.contiguous()
+    B, N = int(w.shape[0]), int(w.shape[1])
+    nbins = int(nbins) if nbins is not None else N
+    out = torch.empty((B, nbins), dtype=torch.float64, device=w.device)
+    lib = _lib.load()
+    with torch.cuda.device(w.device):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(w.device).cuda_stream)
+        _lib.check(lib.kf_energy_spectrum(_lib.KF_F32 if w.dtype == torch.complex64 else _lib.KF_F64, N, B,
+                                          ctypes.c_void_p(w.data_ptr()), ctypes.c_void_p(out.data_ptr()), nbins,
+                                          stream), "kf_energy_spectrum")
+    return out[0] if squeeze else out
+
+
+def compute_velocity_fft(omega_hat: torch.Tensor):
+    """utils.py:53-69 on integer wavenumbers (2 pi kx = p, 2 pi ky = q): u_hat = i q psi_hat, v_hat = -i p psi_hat."""
+    N = omega_hat.shape[-2]
+    rd = torch.float32 if omega_hat.dtype == torch.complex64 else torch.float64
+    p = torch.fft.fftfreq(N, 1.0 / N, device=omega_hat.device, dtype=rd)[:, None]
+    q = torch.arange(N // 2 + 1, device=omega_hat.device, dtype=rd)[None, :]
+    k2 = p * p + q * q
+    k2[0, 0] = 1.0
+    psi = omega_hat / k2
+    return 1j * q * psi, -1j * p * psi
+
+
+def compute_energy_mode(uhat, vhat, kx, ky, n, m):
+    """utils.py:89-101 (kx, ky integer wavenumbers)."""
+    return 0.5 * (uhat[..., kx % n, ky % m].abs() ** 2 + vhat[..., kx % n, ky % m].abs() ** 2) / float(n * m) ** 2
+
+
+def compute_velocity_mode(uhat, vhat, kx, ky, n, m):
+    """utils.py:104-121."""
+    return torch.sqrt((uhat[..., kx % n, ky % m].abs() ** 2 + vhat[..., kx % n, ky % m].abs() ** 2) / float(n * m) ** 2)

@@ -94,6 +94,14 @@ size_t kf_workspace_bytes(kf_handle h);
 /* Environments per chunk actually used. */
 int kf_chunk(kf_handle h);
 
+/* Radial kinetic-energy spectrum of omega_hat_dev [B][N][N/2+1] (dtype KF_F32 / KF_F64, no handle needed):
+ * spectrum_dev [B][nbins] double, bin = round(|k|), per-mode energy as in compute_energy_mode
+ * (hydrogym/jax/utils/utils.py:89-101) with velocities from compute_velocity_fft (utils.py:53-69), the
+ * conjugate half of the spectrum counted through weights 2 on 0 < ky < N/2.  sum over bins = mean kinetic
+ * energy per unit area (when nbins > N/sqrt(2)). */
+int kf_energy_spectrum(int dtype, int N, int B, const void* omega_hat_dev, double* spectrum_dev, int nbins,
+                       void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Slab-decomposed single grid (BASELINE.json configs[4]: one N x N flow over P GPUs, one process per
  * GPU).  The reference has no multi-device path; the arithmetic is the same RK sub-stage

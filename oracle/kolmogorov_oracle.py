@@ -113,6 +113,36 @@ def compute_tke(omega_hat, kx, ky, n):
     return np.sum(avg_tke, axis=(-2, -1))
 
 
+def compute_energy_mode(uhat, vhat, kx, ky, n, m):
+    """U:89-101 -- energy of one mode (kx, ky integer wavenumbers)."""
+    return 0.5 * (np.abs(uhat[..., kx % n, ky % m]) ** 2 + np.abs(vhat[..., kx % n, ky % m]) ** 2) / float(n * m) ** 2
+
+
+def energy_spectrum(omega_hat, kx, ky, nbins=None):
+    """Radial sum of the per-mode energies of U:89-101 over the FULL plane: bin = round(|k|) on integer
+    wavenumbers, the conjugate half (not stored by rfft) counted through weights 2 on 0 < ky < m/2.
+    The binning is test infrastructure of this repo (the reference ships the per-mode quantity only)."""
+    n = omega_hat.shape[-2]
+    mh = omega_hat.shape[-1]
+    m = 2 * (mh - 1)
+    uhat, vhat = compute_velocity_fft(omega_hat, kx, ky)
+    e = 0.5 * (np.abs(uhat) ** 2 + np.abs(vhat) ** 2).astype(np.float64) / float(n * m) ** 2
+    p = np.rint(2 * np.pi * np.asarray(kx, dtype=np.float64))
+    q = np.rint(2 * np.pi * np.asarray(ky, dtype=np.float64))
+    wgt = np.where((q == 0) | (q == mh - 1), 1.0, 2.0)
+    bins = np.floor(np.sqrt(p * p + q * q) + 0.5).astype(np.int64)
+    nbins = int(nbins) if nbins is not None else n
+    out = np.zeros(omega_hat.shape[:-2] + (nbins,), dtype=np.float64)
+    keep = (bins < nbins) & (bins > 0)
+    flat = (e * wgt)[..., keep]
+    idx = bins[keep]
+    for b in range(nbins):
+        sel = idx == b
+        if sel.any():
+            out[..., b] = flat[..., sel].sum(axis=-1)
+    return out
+
+
 class PseudoSpectralNavierStokes2D:
     """K:193-292."""
 

@@ -1,0 +1,80 @@
+"""Slab solver over real NCCL all-to-alls: one process per GPU (needs >= 2 GPUs; skipped otherwise).
+Every rank must reproduce the single-rank result of the same kernels."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _state(N, seed):
+    rng = np.random.default_rng(seed)
+    p = np.abs(np.fft.fftfreq(N, 1.0 / N))[:, None]
+    q = np.arange(N // 2 + 1)[None, :]
+    env = np.exp(-(p * p + q * q) / 64.0) * N * N * 0.3
+    return ((rng.normal(size=(N, N // 2 + 1)) + 1j * rng.normal(size=(N, N // 2 + 1))) * env).astype(np.complex64)
+
+
+def _worker(rank, world, port, N, steps, out):
+    import torch.distributed as dist
+    from hydrogym_b200.slab import SlabKolmogorovSolver
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        w0 = torch.from_numpy(_state(N, 9)).cuda()
+        act = torch.tensor([0.2, -0.4, 0.1, 0.3], device="cuda")
+        sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device=f"cuda:{rank}")
+        assert sl.world == world
+        sl.set_state(w0, act)
+        sl.rk_steps(steps)
+        got = sl.get_state()
+        obs, tke = sl.reward_obs()
+        torch.cuda.synchronize()
+        out.put((rank, got.cpu().numpy(), obs.cpu().numpy(), float(tke)))
+        sl.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("N", [1024])
+def test_slab_nccl_matches_single_rank(N):
+    world = torch.cuda.device_count()
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs")
+    world = 2 if world < 4 else (4 if world < 8 else 8)
+    import torch.multiprocessing as mp
+    from hydrogym_b200.slab import SlabKolmogorovSolver
+    steps = 2
+    sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device="cuda:0", local_ranks=1)
+    sl.set_state(torch.from_numpy(_state(N, 9)).cuda(), torch.tensor([0.2, -0.4, 0.1, 0.3], device="cuda"))
+    sl.rk_steps(steps)
+    want = sl.get_state().cpu().numpy()
+    wobs, wtke = sl.reward_obs()
+    wobs, wtke = wobs.cpu().numpy(), float(wtke)
+    sl.close()
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, N, steps, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [out.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, got, obs, tke in res:
+        err = np.linalg.norm(got - want) / np.linalg.norm(want)
+        assert err < 1e-6, (rank, err)  # same kernels, same order of operations per element
+        assert np.abs(obs - wobs).max() < 1e-5 * max(1.0, np.abs(wobs).max())
+        assert abs(tke - wtke) < 1e-6 * max(1.0, abs(wtke))

@@ -118,3 +118,28 @@ def test_batched_equals_looped():
     for b in range(3):
         chb = env.equation.control_term(w0[b], env._control_field(acts[b], env.default_params))
         assert np.allclose(both[b], env.integrator.rk_steps(w0[b], 3, chb), rtol=1e-12)
+
+
+def test_energy_spectrum_sums_to_kinetic_energy():
+    """The radial spectrum (oracle binning of utils.py:89-101 per-mode energies) sums to the physical-space
+    kinetic energy 0.5 <u^2 + v^2> when the Nyquist lines are empty (Parseval)."""
+    N = 32
+    env = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=np.float64)
+    rng = np.random.default_rng(0)
+    w = rng.normal(size=(N, N))
+    wh = np.fft.rfft2(w)
+    wh[N // 2, :] = 0
+    wh[:, N // 2] = 0
+    wh[0, 0] = 0
+    spec = orc.energy_spectrum(wh, env.kx, env.ky)
+    uh, vh = orc.compute_velocity_fft(wh, env.kx, env.ky)
+    u, v = np.fft.irfft2(uh), np.fft.irfft2(vh)
+    assert spec.shape == (N,)
+    assert abs(spec.sum() - 0.5 * np.mean(u * u + v * v)) < 1e-12 * spec.sum()
+    # one mode: matches compute_energy_mode on that mode and its conjugate
+    one = np.zeros_like(wh)
+    one[3, 4] = 2.0 - 1.0j
+    s1 = orc.energy_spectrum(one, env.kx, env.ky)
+    uh, vh = orc.compute_velocity_fft(one, env.kx, env.ky)
+    assert abs(s1[5] - 2 * orc.compute_energy_mode(uh, vh, 3, 4, N, N)) < 1e-18
+    assert s1.sum() == s1[5]

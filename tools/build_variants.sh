@@ -4,7 +4,7 @@ cd "$(dirname "$0")/.." && mkdir -p variants
 while [ $# -gt 1 ]; do
   name=$1; flags=$2; shift 2
   ( nvcc -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo -Xcompiler -fPIC -shared $flags \
-      hydrogym_b200/csrc/kolmo_b200.cu -o variants/lib_$name.so 2> variants/$name.log || echo "FAILED $name" ) &
+      hydrogym_b200/csrc/kolmo_b200.cu build/slab.cu.o build/diag.cu.o -o variants/lib_$name.so 2> variants/$name.log || echo "FAILED $name" ) &
 done
 wait
 ls -la variants/*.so
