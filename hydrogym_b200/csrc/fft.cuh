@@ -21,6 +21,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cmath>
+
 namespace kf {
 
 // ---------------------------------------------------------------------------
@@ -237,6 +239,12 @@ template <int R> struct Radix {
 template <int L_, int TPF_, int R0_, int R1_, int R2_ = 1, int R3_ = 1> struct Plan {
   static constexpr int L = L_, TPF = TPF_, E = L_ / TPF_;
   __host__ __device__ static constexpr int radix(int p) { return p == 0 ? R0_ : p == 1 ? R1_ : p == 2 ? R2_ : R3_; }
+  // Twiddles live in a TRANSPOSED table: pass p >= 1 (sub-transform length NS, radix R) owns the block
+  // [r - 1][k] = exp(-2*pi*i * r*k / (NS*R)), r = 1..R-1, k = 0..NS-1, at offset tw_off(p).  Threads of one FFT
+  // have consecutive k, so every twiddle load is a run of consecutive words (no bank conflicts, unlike
+  // tw[r*k*stride] in a linear table).  Total size sum (R-1)*NS = L - R0 <= L.
+  __host__ __device__ static constexpr int ns(int p) { return p == 0 ? 1 : ns(p - 1) * radix(p - 1); }
+  __host__ __device__ static constexpr int tw_off(int p) { return p <= 1 ? 0 : tw_off(p - 1) + (radix(p - 1) - 1) * ns(p - 1); }
   static_assert(R0_ * R1_ * R2_ * R3_ == L_, "radices must multiply to L");
   static_assert(E % R0_ == 0 && E % R1_ == 0 && E % R2_ == 0 && E % R3_ == 0, "radix must divide E");
 };
@@ -263,7 +271,7 @@ template <class P, int PASS, int NS, int DIR, typename T, class Ex> struct PassR
       if (NS > 1) {
 #pragma unroll
         for (int r = 1; r < R; ++r) {
-          Cx<S> w = ldc(tw + r * k * (P::L / (NS * R)));
+          Cx<S> w = ldc(tw + P::tw_off(PASS) + (r - 1) * NS + k);
           if (DIR > 0) w.y = -w.y;
           a[r] = cmul_tw<T>(a[r], w);
         }
@@ -313,6 +321,24 @@ template <class P, int PASS, int NS, int DIR, typename T, class Ex> struct PassR
     }
   }
 };
+
+// Host side: fill the transposed twiddle table of plan P (L complex numbers as interleaved doubles).
+template <class P> inline void fill_twiddles(double* out) {
+  const double kPi = 3.14159265358979323846264338327950288;
+  for (int i = 0; i < 2 * P::L; ++i) out[i] = 0.0;
+  int off = 0, ns = P::radix(0);
+  for (int p = 1; p < 4 && ns < P::L; ++p) {
+    const int R = P::radix(p);
+    for (int r = 1; r < R; ++r)
+      for (int k = 0; k < ns; ++k) {
+        const double ang = -2.0 * kPi * (double)r * (double)k / ((double)ns * R);
+        out[2 * (off + (r - 1) * ns + k)] = cos(ang);
+        out[2 * (off + (r - 1) * ns + k) + 1] = sin(ang);
+      }
+    off += (R - 1) * ns;
+    ns *= R;
+  }
+}
 
 // In-register FFT over the TPF threads that share `ex`.  v[m] <-> element t + TPF*m.
 // Unnormalised in both directions.

@@ -51,6 +51,7 @@ struct Ops {
   int tc, col_threads, row_groups, row_threads;
   size_t col_smem, row_smem;
   cudaError_t (*prepare)();
+  void (*fill_tw)(double* re_im);  // transposed twiddle table of the plan (fft.cuh), N complex
   // TMA-fed persistent column kernel of the RK sub-stage: set-up (tensor maps, grid) and launch
   int (*tma_setup)(struct Ctx&);
   void (*col_tma)(const struct Ctx&, int nb, const Stage&, cudaStream_t);
@@ -175,7 +176,7 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     o.elem = sizeof(C);
     o.tc = TC; o.col_threads = P::TPF * TC; o.row_groups = GROUPS; o.row_threads = P::TPF * GROUPS;
     o.col_smem = col_smem(); o.row_smem = row_smem();
-    o.prepare = prepare; o.tma_setup = tma_setup; o.col_tma = col_tma; o.col = col; o.row = row; o.obs = obs; o.finalize = finalize;
+    o.prepare = prepare; o.fill_tw = kf::fill_twiddles<P>; o.tma_setup = tma_setup; o.col_tma = col_tma; o.col = col; o.row = row; o.obs = obs; o.finalize = finalize;
     o.import_ = import_; o.export_ = export_; o.forcing = forcing;
     return o;
   }
@@ -482,11 +483,7 @@ int kf_create(kf_handle* out, const kf_config* cfg) {
   if (!rc) {
     // twiddles exp(-2*pi*i*m/N), computed in fp64 and rounded once
     std::vector<double> t64(2 * (size_t)c.N);
-    const double kPi = 3.14159265358979323846264338327950288;
-    for (int m = 0; m < c.N; ++m) {
-      t64[2 * m] = std::cos(2.0 * kPi * m / c.N);
-      t64[2 * m + 1] = -std::sin(2.0 * kPi * m / c.N);
-    }
+    ops->fill_tw(t64.data());  // computed in fp64, rounded once
     cudaError_t e;
     if (cfg->dtype == KF_F32) {
       std::vector<float> t32(t64.begin(), t64.end());

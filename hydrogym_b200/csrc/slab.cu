@@ -34,6 +34,7 @@ struct SlabCtx;
 struct SlabOps {
   size_t elem;  // bytes per complex
   cudaError_t (*prepare)();
+  void (*fill_tw)(double* re_im);  // transposed twiddle table of the plan (fft.cuh), N complex
   void (*col)(const SlabCtx&, int stage, const void* adv_recv, void* fld_send, cudaStream_t);
   void (*row)(const SlabCtx&, const void* fld_recv, void* adv_send, cudaStream_t);
   void (*obs)(const SlabCtx&, const void* fld_recv, double* acc, void* obs, double obs_w, cudaStream_t);
@@ -155,7 +156,7 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
   static SlabOps make() {
     SlabOps o;
     o.elem = sizeof(C);
-    o.prepare = prepare; o.col = col; o.row = row; o.obs = obs;
+    o.prepare = prepare; o.fill_tw = kf::fill_twiddles<P>; o.col = col; o.row = row; o.obs = obs;
     o.import_ = import_; o.export_ = export_; o.forcing = forcing;
     return o;
   }
@@ -262,11 +263,7 @@ int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks) {
   if (!rc) rc = dev_alloc(c, &c.C, el * 4 * (c.MH + 1));
   if (!rc) {
     std::vector<double> t64(2 * (size_t)c.N);
-    const double kPi = 3.14159265358979323846264338327950288;
-    for (int m = 0; m < c.N; ++m) {
-      t64[2 * m] = std::cos(2.0 * kPi * m / c.N);
-      t64[2 * m + 1] = -std::sin(2.0 * kPi * m / c.N);
-    }
+    ops->fill_tw(t64.data());  // computed in fp64, rounded once
     cudaError_t e;
     if (cfg->dtype == KF_F32) {
       std::vector<float> t32(t64.begin(), t64.end());
