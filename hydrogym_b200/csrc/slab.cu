@@ -167,7 +167,11 @@ const SlabOps* find_slab_ops(int dtype, int N) {
   static const SlabOps f256 = SlabImpl<float, Plan<256, 16, 16, 16>, 8, 8>::make();
   static const SlabOps f1024 = SlabImpl<float, Plan<1024, 64, 16, 4, 16>, 2, 2>::make();
   static const SlabOps f4096 = SlabImpl<float, Plan<4096, 256, 16, 16, 16>, 1, 1>::make();
+#ifdef KF_SLAB_E32
+  static const SlabOps f8192 = SlabImpl<float, Plan<8192, 256, 32, 16, 16>, 1, 1>::make();
+#else
   static const SlabOps f8192 = SlabImpl<float, Plan<8192, 512, 16, 16, 2, 16>, 1, 1>::make();
+#endif
   static const SlabOps d256 = SlabImpl<double, Plan<256, 32, 8, 4, 8>, 4, 4>::make();
   static const SlabOps d1024 = SlabImpl<double, Plan<1024, 128, 8, 2, 8, 8>, 1, 1>::make();
   const bool f = dtype == KF_F32;
