@@ -52,6 +52,12 @@ struct SlabCtx {
   size_t bytes = 0;
   long long launches = 0;
   bool have_constants = false;
+  // peer-to-peer exchange: library-owned receive buffers and the peers' buffers mapped into this process
+  void *own_fld = nullptr, *own_adv = nullptr;
+  void* peer_fld[KF_MAX_PEERS] = {};
+  void* peer_adv[KF_MAX_PEERS] = {};
+  bool ipc_opened[KF_MAX_PEERS] = {};
+  bool p2p = false;
 };
 
 template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
@@ -80,7 +86,8 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
     a.wk = (C*)c.wk; a.hk = (C*)c.hk; a.wnyq = (C*)c.wnyq; a.hnyq = (C*)c.hnyq;
     a.G = (const C*)c.G; a.advk = (const C*)c.advk;
     a.fak = (C2*)c.fk; a.fbk = a.fak + (size_t)c.Q * N;
-    a.fax = nullptr; a.fbx = nullptr; a.fblk = 2 * (size_t)c.X * c.Q; a.advx = nullptr;
+    a.fax = nullptr; a.fbx = nullptr; a.fblk = 2 * (size_t)c.X * c.Q;
+    for (int d = 0; d < KF_MAX_PEERS; ++d) a.adv_dst[d] = nullptr;
     a.tw = (const C*)c.tw;
     a.beta = 0; a.gdt = 0; a.munu = 0;
     a.scale = (T)(1.0 / ((double)N * (double)N));
@@ -102,8 +109,8 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
     const int Q = c.Q, X = c.X;
     if (stage >= 0) {
       // adv_recv [P][X][Q] is [N][Q] with plain rows -> advk [Q][N]
-      kf::TransposeArgs p{N, Q, N, Q, 0, (size_t)Q, 0, 0, (size_t)N, 0};
-      transpose<C>((const C*)adv_recv, (C*)c.advk, p, 1, s);
+      kf::TransposeArgs p{N, Q, N, Q, 0, (size_t)Q, 0, 0, (size_t)N, 0, {}};
+      transpose<C>((const C*)(adv_recv ? adv_recv : c.own_adv), (C*)c.advk, p, 1, s);
       a.beta = (T)kBeta[stage];
       a.gdt = (T)(kGamma[stage] * c.cfg.dt);                                        // base.py:55
       a.munu = (T)(0.5 * c.cfg.dt * (kAlpha[stage + 1] - kAlpha[stage]) * c.cfg.nu);  // base.py:54
@@ -113,22 +120,27 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
       if (c.rank == 0) kf::slab_col_kernel<T, P, 1, kf::kSlabInit, true, 1><<<1, P::TPF, smem(1), s>>>(a);
       kf::slab_col_kernel<T, P, GROUPS, kf::kSlabInit, false, 1><<<Q / GROUPS, P::TPF * GROUPS, smem(GROUPS), s>>>(a);
     }
-    // fak, fbk [Q][N] -> send [P][2][X][Q]: logical output row x at (x / X) * 2XQ + (x % X) * Q, array z at + z*XQ
-    kf::TransposeArgs p{Q, N, Q, X, 0, (size_t)N, (size_t)Q * N, 2 * (size_t)X * Q, (size_t)Q, (size_t)X * Q};
-    transpose<C2>((const C2*)c.fk, (C2*)fld_send, p, 2, s);
+    // fak, fbk [Q][N] -> blocks [2][X][Q] per destination rank d (rows x in [d*X, (d+1)*X), array z at + z*XQ):
+    // block d of the local send buffer, or slot `rank` of rank d's receive buffer written over NVLink
+    kf::TransposeArgs p{Q, N, Q, X, 0, (size_t)N, (size_t)Q * N, 2 * (size_t)X * Q, (size_t)Q, (size_t)X * Q, {}};
+    for (int d = 0; d < c.P; ++d)
+      p.out_tab[d] = fld_send ? (void*)((C2*)fld_send + (size_t)d * 2 * X * Q)
+                              : (void*)((C2*)c.peer_fld[d] + (size_t)c.rank * 2 * X * Q);
+    transpose<C2>((const C2*)c.fk, (C2*)nullptr, p, 2, s);
   }
 
   static void row(const SlabCtx& c, const void* fld_recv, void* adv_send, cudaStream_t s) {
     kf::SlabArgs<T> a = args(c);
-    a.fax = (const C2*)fld_recv;
+    a.fax = (const C2*)(fld_recv ? fld_recv : c.own_fld);
     a.fbx = a.fax + (size_t)c.X * c.Q;
-    a.advx = (C*)adv_send;
+    for (int d = 0; d < c.P; ++d)
+      a.adv_dst[d] = adv_send ? (C*)adv_send + (size_t)d * c.X * c.Q : (C*)c.peer_adv[d] + (size_t)c.rank * c.X * c.Q;
     kf::slab_row_kernel<T, P, RGROUPS, 1><<<c.X / 2 / RGROUPS, P::TPF * RGROUPS, smem(RGROUPS), s>>>(a);
   }
 
   static void obs(const SlabCtx& c, const void* fld_recv, double* acc, void* obs_dev, double obs_w, cudaStream_t s) {
     kf::SlabArgs<T> a = args(c);
-    a.fax = (const C2*)fld_recv;
+    a.fax = (const C2*)(fld_recv ? fld_recv : c.own_fld);
     a.fbx = a.fax + (size_t)c.X * c.Q;
     const int st = N / c.cfg.obs_size;
     kf::slab_row_obs_kernel<T, P, RGROUPS><<<c.X / RGROUPS, P::TPF * RGROUPS, smem(RGROUPS), s>>>(
@@ -138,13 +150,13 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
   // user omega_hat [N][M/2+1] (full array on every rank): this rank's columns <-> wk [Q][N], ky = M/2 <-> wnyq
   static void import_(const SlabCtx& c, const void* user, cudaStream_t s) {
     const C* u = (const C*)user;
-    kf::TransposeArgs p{N, c.Q, N, c.Q, 0, (size_t)(MH + 1), 0, 0, (size_t)N, 0};
+    kf::TransposeArgs p{N, c.Q, N, c.Q, 0, (size_t)(MH + 1), 0, 0, (size_t)N, 0, {}};
     transpose<C>(u + (size_t)c.rank * c.Q, (C*)c.wk, p, 1, s);
     if (c.rank == 0) kf::strided_copy_kernel<C><<<(N + 255) / 256, 256, 0, s>>>(u + MH, MH + 1, (C*)c.wnyq, 1, N);
   }
   static void export_(const SlabCtx& c, void* user, cudaStream_t s) {
     C* u = (C*)user;
-    kf::TransposeArgs p{c.Q, N, c.Q, N, 0, (size_t)N, 0, 0, (size_t)(MH + 1), 0};
+    kf::TransposeArgs p{c.Q, N, c.Q, N, 0, (size_t)N, 0, 0, (size_t)(MH + 1), 0, {}};
     transpose<C>((const C*)c.wk, u + (size_t)c.rank * c.Q, p, 1, s);
     if (c.rank == 0) kf::strided_copy_kernel<C><<<(N + 255) / 256, 256, 0, s>>>((const C*)c.wnyq, 1, u + MH, MH + 1, N);
   }
@@ -192,7 +204,13 @@ int dev_alloc(SlabCtx& c, void** p, size_t bytes) {
 }
 
 void free_all(SlabCtx& c) {
-  void* ptrs[] = {c.wk, c.hk, c.wnyq, c.hnyq, c.G, c.advk, c.fk, c.tw, c.F, c.C};
+  for (int d = 0; d < KF_MAX_PEERS; ++d) {
+    if (c.ipc_opened[d]) {
+      cudaIpcCloseMemHandle(c.peer_fld[d]);
+      cudaIpcCloseMemHandle(c.peer_adv[d]);
+    }
+  }
+  void* ptrs[] = {c.wk, c.hk, c.wnyq, c.hnyq, c.G, c.advk, c.fk, c.tw, c.F, c.C, c.own_fld, c.own_adv};
   for (void* p : ptrs)
     if (p) cudaFree(p);
 }
@@ -345,9 +363,11 @@ size_t kf_slab_exchange_bytes(kf_slab h, int which) {
 }
 
 int kf_slab_col(kf_slab h, int stage, const void* adv_recv_dev, void* fld_send_dev, void* stream) {
-  if (!h || !fld_send_dev) return fail("kf_slab_col: null argument");
+  if (!h) return fail("kf_slab_col: null handle");
+  if (!fld_send_dev && !h->c.p2p) return fail("kf_slab_col: no send buffer and no peer-to-peer exchange attached");
   if (stage > 4) return fail("kf_slab_col: stage must be 0..4, or negative for the fields of the stored state");
-  if (stage >= 0 && !adv_recv_dev) return fail("kf_slab_col: a sub-stage needs the received advection blocks");
+  if (stage >= 0 && !adv_recv_dev && !h->c.p2p)
+    return fail("kf_slab_col: a sub-stage needs the received advection blocks");
   SlabCtx& c = h->c;
   if (stage >= 0 && !c.have_constants) return fail("kf_slab_set_constants has not been called");
   DeviceGuard guard(c.cfg.device);
@@ -358,7 +378,9 @@ int kf_slab_col(kf_slab h, int stage, const void* adv_recv_dev, void* fld_send_d
 }
 
 int kf_slab_row(kf_slab h, const void* fld_recv_dev, void* adv_send_dev, void* stream) {
-  if (!h || !fld_recv_dev || !adv_send_dev) return fail("kf_slab_row: null argument");
+  if (!h) return fail("kf_slab_row: null handle");
+  if ((!fld_recv_dev || !adv_send_dev) && !h->c.p2p)
+    return fail("kf_slab_row: null buffer and no peer-to-peer exchange attached");
   SlabCtx& c = h->c;
   DeviceGuard guard(c.cfg.device);
   c.ops->row(c, fld_recv_dev, adv_send_dev, (cudaStream_t)stream);
@@ -368,12 +390,64 @@ int kf_slab_row(kf_slab h, const void* fld_recv_dev, void* adv_send_dev, void* s
 }
 
 int kf_slab_obs(kf_slab h, const void* fld_recv_dev, double* acc4_dev, void* obs_dev, double obs_w, void* stream) {
-  if (!h || !fld_recv_dev || !acc4_dev) return fail("kf_slab_obs: null argument");
+  if (!h || !acc4_dev || (!fld_recv_dev && !h->c.p2p)) return fail("kf_slab_obs: null argument");
   SlabCtx& c = h->c;
   DeviceGuard guard(c.cfg.device);
   c.ops->obs(c, fld_recv_dev, acc4_dev, obs_dev, obs_w, (cudaStream_t)stream);
   c.launches += 1;
   KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// -- peer-to-peer exchange -------------------------------------------------------------------------------
+
+int kf_slab_p2p_init(kf_slab h, void* ipc_handles_out) {
+  if (!h) return fail("kf_slab_p2p_init: null handle");
+  SlabCtx& c = h->c;
+  if (c.P > KF_MAX_PEERS) return fail("kf_slab_p2p_init: too many ranks");
+  DeviceGuard guard(c.cfg.device);
+  const size_t tile = c.ops->elem * (size_t)c.N * c.Q;
+  if (!c.own_fld) {
+    if (int rc = dev_alloc(c, &c.own_fld, 4 * tile)) return rc;
+    if (int rc = dev_alloc(c, &c.own_adv, tile)) return rc;
+  }
+  if (ipc_handles_out) {
+    cudaIpcMemHandle_t* out = (cudaIpcMemHandle_t*)ipc_handles_out;
+    KF_CUDA(cudaIpcGetMemHandle(out + 0, c.own_fld));
+    KF_CUDA(cudaIpcGetMemHandle(out + 1, c.own_adv));
+  }
+  return 0;
+}
+
+int kf_slab_p2p_attach(kf_slab h, const void* all_handles) {
+  if (!h || !all_handles) return fail("kf_slab_p2p_attach: null argument");
+  SlabCtx& c = h->c;
+  if (!c.own_fld) return fail("kf_slab_p2p_attach: call kf_slab_p2p_init first");
+  DeviceGuard guard(c.cfg.device);
+  const cudaIpcMemHandle_t* hs = (const cudaIpcMemHandle_t*)all_handles;
+  for (int d = 0; d < c.P; ++d) {
+    if (d == c.rank) {
+      c.peer_fld[d] = c.own_fld;
+      c.peer_adv[d] = c.own_adv;
+      continue;
+    }
+    KF_CUDA(cudaIpcOpenMemHandle(&c.peer_fld[d], hs[2 * d + 0], cudaIpcMemLazyEnablePeerAccess));
+    KF_CUDA(cudaIpcOpenMemHandle(&c.peer_adv[d], hs[2 * d + 1], cudaIpcMemLazyEnablePeerAccess));
+    c.ipc_opened[d] = true;
+  }
+  c.p2p = true;
+  return 0;
+}
+
+int kf_slab_p2p_attach_local(kf_slab h, const kf_slab* peers) {
+  if (!h || !peers) return fail("kf_slab_p2p_attach_local: null argument");
+  SlabCtx& c = h->c;
+  for (int d = 0; d < c.P; ++d) {
+    if (!peers[d] || !peers[d]->c.own_fld) return fail("kf_slab_p2p_attach_local: peer without receive buffers");
+    c.peer_fld[d] = peers[d]->c.own_fld;
+    c.peer_adv[d] = peers[d]->c.own_adv;
+  }
+  c.p2p = true;
   return 0;
 }
 

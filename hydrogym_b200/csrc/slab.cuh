@@ -19,6 +19,10 @@
 
 namespace kf {
 
+#ifndef KF_MAX_PEERS
+#define KF_MAX_PEERS 16
+#endif
+
 template <typename T> struct SlabArgs {
   using L2 = typename PairOf<T>::type;
   // K layout
@@ -34,7 +38,10 @@ template <typename T> struct SlabArgs {
   const Cx<L2>* fax;    // fields received from the peers
   const Cx<L2>* fbx;
   size_t fblk;          // block stride of fax / fbx (2*X*Q: fa and fb of one peer are adjacent)
-  Cx<T>* advx;          // advection rows to send, block stride X*Q
+  // advection rows leave in blocks of Q columns: block d (the columns rank d owns) starts at adv_dst[d] and is
+  // [X][Q] -- a slice of the local send buffer (NCCL all-to-all follows) or of rank d's receive buffer mapped
+  // over NVLink (peer-to-peer stores straight from this kernel, no separate collective)
+  Cx<T>* adv_dst[KF_MAX_PEERS];
   const Cx<T>* tw;      // [N] exp(-2*pi*i*m/N)
   T beta, gdt, munu, scale;
   int dealias;
@@ -225,13 +232,11 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_row_kernel(SlabArgs
 #pragma unroll
   for (int m = 0; m < E; ++m) ex1.store(t + TPF * m, v[m]);
   ex1.sync();
-  const size_t ablk = (size_t)a.X * Q;
-  Cx<T>* o0 = a.advx + (size_t)xl0 * Q;
-  Cx<T>* o1 = o0 + Q;
 #pragma unroll
   for (int m = 0; m < E / 2; ++m) {
     const int k = t + TPF * m;
-    const size_t off = (size_t)(k >> lgQ) * ablk + (k & (Q - 1));
+    Cx<T>* o0 = a.adv_dst[k >> lgQ] + (size_t)xl0 * Q + (k & (Q - 1));
+    Cx<T>* o1 = o0 + Q;
     if (k == 0) {
       const Cx<T> wn = ex1.load(MH);
       stc(o0, mk<T>(v[m].x, wn.x));
@@ -239,8 +244,8 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_row_kernel(SlabArgs
     } else {
       const Cx<T> wm = ex1.load(M - k);
       const Cx<T> s = add_conj(v[m], wm), d = sub_conj(v[m], wm);
-      stc(o0 + off, (T)0.5 * s);
-      stc(o1 + off, mk<T>((T)0.5 * d.y, (T)-0.5 * d.x));
+      stc(o0, (T)0.5 * s);
+      stc(o1, mk<T>((T)0.5 * d.y, (T)-0.5 * d.x));
     }
   }
 }
@@ -314,6 +319,9 @@ struct TransposeArgs {
   int in_rpb, out_rpb;
   size_t in_blk, in_ld, in_z;
   size_t out_blk, out_ld, out_z;
+  // if out_tab[0] != nullptr, output block j (logical rows j*out_rpb ...) starts at out_tab[j] instead of
+  // out + j*out_blk: the blocks may live on different GPUs (peer-mapped receive buffers)
+  void* out_tab[KF_MAX_PEERS];
 };
 
 template <typename V> __global__ void __launch_bounds__(256) transpose_kernel(const V* __restrict__ in, V* __restrict__ out,
@@ -332,8 +340,12 @@ template <typename V> __global__ void __launch_bounds__(256) transpose_kernel(co
 #pragma unroll
   for (int i = 0; i < 32; i += 8) {
     const int c = c0 + ty + i, r = r0 + tx;
-    if (r < p.R && c < p.Cn)
-      out[(size_t)(c / p.out_rpb) * p.out_blk + (size_t)(c % p.out_rpb) * p.out_ld + r] = tile[tx][ty + i];
+    if (r < p.R && c < p.Cn) {
+      const int blk = c / p.out_rpb;
+      V* dst = p.out_tab[0] ? reinterpret_cast<V*>(p.out_tab[blk]) + (size_t)blockIdx.z * p.out_z
+                            : out + (size_t)blk * p.out_blk;
+      dst[(size_t)(c % p.out_rpb) * p.out_ld + r] = tile[tx][ty + i];
+    }
   }
 }
 

@@ -33,12 +33,19 @@ def _ptr(t):
 class _SlabRank:
     """One rank's ``kf_slab`` handle and its four exchange buffers."""
 
-    def __init__(self, lib, cfg, rank, nranks, dtype, device, forcing_row, control_rows):
+    def __init__(self, lib, cfg, rank, nranks, dtype, device, forcing_row, control_rows, p2p=False):
         self.lib, self.rank, self.nranks = lib, rank, nranks
         self.h = ctypes.c_void_p(0)
         _lib.check(lib.kf_slab_create(ctypes.byref(self.h), ctypes.byref(cfg), rank, nranks), "kf_slab_create")
         _lib.check(lib.kf_slab_set_constants(self.h, forcing_row.ctypes.data_as(ctypes.c_void_p),
                                              control_rows.ctypes.data_as(ctypes.c_void_p)), "kf_slab_set_constants")
+        self.acc = torch.zeros(4, dtype=torch.float64, device=device)
+        self.ipc = None
+        if p2p:  # receive buffers live in the library (cudaMalloc: exportable through CUDA IPC); no send buffers
+            self.ipc = (ctypes.c_ubyte * 128)()
+            _lib.check(lib.kf_slab_p2p_init(self.h, ctypes.byref(self.ipc)), "kf_slab_p2p_init")
+            self.fld_send = self.fld_recv = self.adv_send = self.adv_recv = None
+            return
         real = 4 if dtype == torch.float32 else 8
         nf = lib.kf_slab_exchange_bytes(self.h, 0) // real
         na = lib.kf_slab_exchange_bytes(self.h, 1) // real
@@ -49,7 +56,6 @@ class _SlabRank:
         else:
             self.fld_recv = torch.zeros(nf, dtype=dtype, device=device)
             self.adv_recv = torch.zeros(na, dtype=dtype, device=device)
-        self.acc = torch.zeros(4, dtype=torch.float64, device=device)
 
     def close(self):
         if self.h.value:
@@ -62,7 +68,9 @@ class SlabKolmogorovSolver:
 
     def __init__(self, grid_size=(8192, 8192), Re=1000, k=4, control_ks=(4, 5, 6, 7), dt=1e-3,
                  dtype=torch.float32, device=None, dealias=False, obs_size=8, min_action=-0.5, max_action=0.5,
-                 domain_y=(0, 2 * np.pi), group=None, local_ranks=None, zero_forcing=False):
+                 domain_y=(0, 2 * np.pi), group=None, local_ranks=None, zero_forcing=False, exchange="nccl"):
+        if exchange not in ("nccl", "p2p"):
+            raise ValueError("exchange must be 'nccl' (all_to_all_single) or 'p2p' (stores into peer-mapped buffers)")
         if dtype not in (torch.float32, torch.float64):
             raise ValueError("dtype must be torch.float32 or torch.float64")
         N, M = grid_size
@@ -87,6 +95,8 @@ class SlabKolmogorovSolver:
                 self.world, my_ranks = dist.get_world_size(group), [dist.get_rank(group)]
             else:
                 self.world, my_ranks = 1, [0]
+        self.p2p = exchange == "p2p"
+        self._flag = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._lib = _lib.load()
         cfg = _lib.KfConfig(N=N, M=M, B=1, dtype=_lib.KF_F32 if dtype == torch.float32 else _lib.KF_F64,
                             nu=self.nu, dt=self.dt, n_inner=1, n_outer=1, dealias=int(bool(dealias)), drag=0.0,
@@ -102,7 +112,9 @@ class SlabKolmogorovSolver:
         with torch.cuda.device(self.device):
             for r in my_ranks:
                 self._ranks.append(_SlabRank(self._lib, cfg, r, self.world, dtype, self.device, forcing_row,
-                                             control_rows))
+                                             control_rows, p2p=self.p2p))
+            if self.p2p:
+                self._attach_peers()
         self.rk_steps_done = 0
 
     # -- plumbing --------------------------------------------------------------
@@ -120,8 +132,39 @@ class SlabKolmogorovSolver:
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
+    def _attach_peers(self):
+        """Map every rank's receive buffers into every other rank (CUDA IPC over NVLink, or raw pointers when the
+        ranks are emulated in this process)."""
+        if self.local:
+            arr = (ctypes.c_void_p * self.world)(*[r.h for r in self._ranks])
+            for r in self._ranks:
+                _lib.check(self._lib.kf_slab_p2p_attach_local(r.h, arr), "kf_slab_p2p_attach_local")
+            return
+        r = self._ranks[0]
+        mine = torch.frombuffer(bytearray(bytes(r.ipc)), dtype=torch.uint8).to(self.device)
+        if self.world > 1:
+            allh = torch.empty(self.world * 128, dtype=torch.uint8, device=self.device)
+            dist.all_gather_into_tensor(allh, mine, group=self.group)
+        else:
+            allh = mine
+        blob = allh.cpu().numpy().tobytes()
+        buf = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
+        _lib.check(self._lib.kf_slab_p2p_attach(r.h, ctypes.byref(buf)), "kf_slab_p2p_attach")
+        if self.world > 1:
+            dist.barrier(group=self.group)
+
+    def _rank_barrier(self):
+        """Stream-ordered cross-rank barrier: every rank's earlier kernels (and their peer stores) are complete
+        before any rank's later kernels start."""
+        if not self.local and self.world > 1:
+            dist.all_reduce(self._flag, group=self.group)
+
     def _all_to_all(self, which):
-        """Block d of every rank's send buffer goes to rank d; block s of a recv buffer comes from rank s."""
+        """Block d of every rank's send buffer goes to rank d; block s of a recv buffer comes from rank s.
+        In peer-to-peer mode the producing kernels have already stored the blocks remotely: only a barrier."""
+        if self.p2p:
+            self._rank_barrier()
+            return
         if self.world == 1:
             return
         if self.local:
@@ -152,7 +195,8 @@ class SlabKolmogorovSolver:
     def workspace_bytes(self):
         per = [int(self._lib.kf_slab_workspace_bytes(r.h)) +
                sum(t.numel() * t.element_size() for t in {id(t): t for t in
-                                                          (r.fld_send, r.fld_recv, r.adv_send, r.adv_recv)}.values())
+                                                          (r.fld_send, r.fld_recv, r.adv_send, r.adv_recv)
+                                                          if t is not None}.values())
                for r in self._ranks]
         return max(per)
 
@@ -168,6 +212,8 @@ class SlabKolmogorovSolver:
                 raise ValueError("action must have shape (4,)")
         with torch.cuda.device(self.device):
             s = self._stream()
+            if self.p2p:
+                self._rank_barrier()  # nobody is still reading the receive buffers the transposes will overwrite
             for r in self._ranks:
                 _lib.check(self._lib.kf_slab_import(r.h, _ptr(omega_hat), s), "kf_slab_import")
                 _lib.check(self._lib.kf_slab_set_action(r.h, _ptr(action), s), "kf_slab_set_action")

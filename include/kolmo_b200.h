@@ -139,6 +139,17 @@ int kf_slab_row(kf_slab h, const void* fld_recv_dev, void* adv_send_dev, void* s
  * obs_w * |velocity| at the probes on this rank's rows.  The host sums both over the ranks
  * (compute_tke utils.py:175-194, _trajectory_mean_obs kolmogorov.py:426-446). */
 int kf_slab_obs(kf_slab h, const void* fld_recv_dev, double* acc4_dev, void* obs_dev, double obs_w, void* stream);
+/* Peer-to-peer exchange (instead of the two all-to-alls): the library owns one receive buffer per direction;
+ * kf_slab_p2p_init allocates them and writes their two cudaIpcMemHandle_t (2 x 64 bytes) to ipc_handles_out (may
+ * be NULL); after the host has gathered all ranks' handles (rank order, [P][128] bytes) kf_slab_p2p_attach maps the
+ * peers' buffers over NVLink.  Then kf_slab_row / kf_slab_col / kf_slab_obs accept NULL exchange buffers: the row
+ * kernel stores its advection blocks and the column pass's transposes store the field blocks DIRECTLY into the
+ * owning rank's receive buffer, so the transfer overlaps the kernel that produces the data.  The host must
+ * separate the two phases of a sub-stage with a cross-rank barrier on the stream (a 1-element NCCL all-reduce).
+ * kf_slab_p2p_attach_local wires P handles living in ONE process (emulated ranks, tests). */
+int kf_slab_p2p_init(kf_slab h, void* ipc_handles_out);
+int kf_slab_p2p_attach(kf_slab h, const void* all_handles);
+int kf_slab_p2p_attach_local(kf_slab h, const kf_slab* peers);
 long long kf_slab_launch_count(kf_slab h);
 size_t kf_slab_workspace_bytes(kf_slab h);
 

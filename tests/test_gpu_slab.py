@@ -58,6 +58,26 @@ def test_slab_1024_matches_batched_kernels(dtype, tol):
         assert rel_l2(got, want) < tol, (P, rel_l2(got, want))
 
 
+@pytest.mark.parametrize("P", [1, 2, 8])
+def test_slab_p2p_exchange_matches_all_to_all(P):
+    """Peer-to-peer mode (kernels store straight into the owning rank's receive buffer) vs the all-to-all mode."""
+    N, steps = 256, 2
+    ref = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=np.float64)
+    w0 = torch.from_numpy(random_states(ref, 1, seed=4).astype(np.complex128)[0]).cuda()
+    act = torch.tensor(ACTION, dtype=torch.float64, device="cuda")
+    out = {}
+    for mode in ("nccl", "p2p"):
+        sl = make_slab(N, 100, torch.float64, P, exchange=mode)
+        sl.set_state(w0, act)
+        sl.rk_steps(steps)
+        obs, tke = sl.reward_obs()
+        out[mode] = (sl.get_state().cpu().numpy(), obs.cpu().numpy(), float(tke))
+        sl.close()
+    assert np.array_equal(out["nccl"][0], out["p2p"][0])
+    assert np.abs(out["nccl"][1] - out["p2p"][1]).max() < 1e-13
+    assert abs(out["nccl"][2] - out["p2p"][2]) < 1e-13
+
+
 @pytest.mark.parametrize("P", [1, 4])
 def test_slab_reward_obs_matches_oracle(P):
     N = 256

@@ -24,7 +24,7 @@ def _state(N, seed):
     return ((rng.normal(size=(N, N // 2 + 1)) + 1j * rng.normal(size=(N, N // 2 + 1))) * env).astype(np.complex64)
 
 
-def _worker(rank, world, port, N, steps, out):
+def _worker(rank, world, port, N, steps, exchange, out):
     import torch.distributed as dist
     from hydrogym_b200.slab import SlabKolmogorovSolver
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -34,7 +34,8 @@ def _worker(rank, world, port, N, steps, out):
     try:
         w0 = torch.from_numpy(_state(N, 9)).cuda()
         act = torch.tensor([0.2, -0.4, 0.1, 0.3], device="cuda")
-        sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device=f"cuda:{rank}")
+        sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device=f"cuda:{rank}",
+                                  exchange=exchange)
         assert sl.world == world
         sl.set_state(w0, act)
         sl.rk_steps(steps)
@@ -47,8 +48,9 @@ def _worker(rank, world, port, N, steps, out):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("exchange", ["nccl", "p2p"])
 @pytest.mark.parametrize("N", [1024])
-def test_slab_nccl_matches_single_rank(N):
+def test_slab_nccl_matches_single_rank(N, exchange):
     world = torch.cuda.device_count()
     if world < 2:
         pytest.skip("needs at least 2 GPUs")
@@ -66,7 +68,7 @@ def test_slab_nccl_matches_single_rank(N):
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, N, steps, out)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, N, steps, exchange, out)) for r in range(world)]
     for p in procs:
         p.start()
     res = [out.get(timeout=600) for _ in range(world)]

@@ -41,7 +41,7 @@ def test_step_counts_and_end_time_guard():
 def test_library_exports_every_declared_symbol():
     from hydrogym_b200 import _lib
     header = open(os.path.join(ROOT, "include", "kolmo_b200.h")).read()
-    declared = set(re.findall(r"\b(kf_[a-z_]+)\s*\(", header))
+    declared = set(re.findall(r"\b(kf_[a-z0-9_]+)\s*\(", header))
     assert declared == set(_lib.SYMBOLS)
     lib = ctypes.CDLL(_lib.LIB_PATH)
     for name in declared:

@@ -11,6 +11,7 @@ def main():
     ap.add_argument("--grid", type=int, default=8192)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p"])
     ap.add_argument("--dt", type=float, default=0.0, help="0 = CFL-safe default 0.8/N (1e-4 at 8192)")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -21,7 +22,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N = a.grid
     dt = a.dt if a.dt > 0 else 0.8 / N  # u ~ 1: CFL = u dt N / (2 pi) ~ 0.13
-    sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device=f"cuda:{local}", dealias=True, dt=dt)
+    sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device=f"cuda:{local}", dealias=True, dt=dt, exchange=a.exchange)
     g = torch.Generator(device="cuda").manual_seed(0)
     w = torch.randn(N, N // 2 + 1, dtype=torch.complex64, device="cuda", generator=g)
     p = torch.fft.fftfreq(N, 1.0 / N, device="cuda")[:, None]; q = torch.arange(N // 2 + 1, device="cuda")[None, :]
@@ -41,7 +42,7 @@ def main():
     obs, tke = sl.reward_obs()
     C = N * (N // 2 + 1) * 8
     if rank == 0:
-        print(json.dumps({"metric": "RK steps/s (single grid, slab-decomposed)", "grid": N, "n_gpus": world, "dt": dt, "rk_steps_run": a.steps + a.warmup,
+        print(json.dumps({"metric": "RK steps/s (single grid, slab-decomposed)", "grid": N, "n_gpus": world, "exchange": a.exchange, "dt": dt, "rk_steps_run": a.steps + a.warmup,
                           "ms_per_rk_step": float(ms), "value": 1e3 / float(ms), "unit": "RK steps/s",
                           "algorithmic_GBps_per_gpu": 70 * C / world / float(ms) / 1e6,
                           "a2a_bytes_per_gpu_per_step": 5 * 5 * C // world * (world - 1) // world,
