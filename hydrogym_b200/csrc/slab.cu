@@ -64,7 +64,7 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
   using C = kf::Cx<T>;
   using C2 = kf::Cx<typename kf::PairOf<T>::type>;
   static constexpr int N = P::L, MH = N / 2;
-  static size_t smem(int groups) { return sizeof(C) * (groups * kf::slab_exchange_elems<N>() + (size_t)N); }
+  static size_t smem(int groups) { return sizeof(C2) * groups * kf::slab_exchange_elems<N>() + sizeof(C) * (size_t)N; }
 
   static cudaError_t prepare() {
     cudaError_t e;

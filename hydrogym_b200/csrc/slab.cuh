@@ -64,8 +64,10 @@ template <typename X, int TPF> struct RowExSplit {
 
 template <int N> __host__ __device__ constexpr size_t slab_exchange_elems() { return (size_t)N + N / 16; }
 // per-CTA shared memory of the slab FFT kernels: one exchange buffer per group + the twiddle table
+// (whole lane-paired complex numbers: the non-split exchange needs half the barriers and 2*E fewer registers
+// than the split one, and 8192 x 16 B + twiddles still fits the 227 KB of an SM)
 template <typename T, int N, int GROUPS> __host__ __device__ constexpr size_t slab_smem_bytes() {
-  return sizeof(Cx<T>) * (GROUPS * slab_exchange_elems<N>() + (size_t)N);
+  return sizeof(Cx<typename PairOf<T>::type>) * GROUPS * slab_exchange_elems<N>() + sizeof(Cx<T>) * (size_t)N;
 }
 
 enum SlabColMode { kSlabStage = 0, kSlabInit = 1 };
@@ -83,14 +85,13 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
   using L2 = typename PairOf<T>::type;
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
   constexpr size_t EXN = slab_exchange_elems<N>();
-  static_assert(sizeof(Cx<T>) == sizeof(L2), "scalar-complex and lane-pair exchange buffers coincide");
   static_assert(!SPECIAL || GROUPS == 1, "the packed column is one CTA");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
-  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<T>);
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<T>));
+  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<L2>);
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
   RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
-  RowExSplit<L2, TPF> ex2{reinterpret_cast<L2*>(s_g)};
+  RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
   const int ql = SPECIAL ? 0 : blockIdx.x * GROUPS + g;
   const int q = a.q0 + ql;
   const bool live = SPECIAL || q != 0;
@@ -202,10 +203,10 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_row_kernel(SlabArgs
   constexpr size_t EXN = slab_exchange_elems<M>();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
-  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<T>);
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<T>));
+  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<L2>);
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
   RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
-  RowExSplit<L2, TPF> ex2{reinterpret_cast<L2*>(s_g)};
+  RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
   const int xl0 = 2 * (blockIdx.x * GROUPS + g);
   const int Q = a.Q, lgQ = a.lgQ;
 
@@ -262,9 +263,9 @@ __global__ void __launch_bounds__(P::TPF* GROUPS) slab_row_obs_kernel(SlabArgs<T
   constexpr size_t EXN = slab_exchange_elems<M>();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
-  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<T>);
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<T>));
-  RowExSplit<L2, TPF> ex2{reinterpret_cast<L2*>(s_g)};
+  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<L2>);
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
+  RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
   const int xl = blockIdx.x * GROUPS + g;
   const int x = a.x0 + xl;
   const int Q = a.Q, lgQ = a.lgQ;
