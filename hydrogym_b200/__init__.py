@@ -7,6 +7,8 @@ from .envs.kolmogorov import (FlowConfig, KolmogorovFlow, KolmogorovFlowParams, 
                               KolmogorovFlowState)
 from .solver import KolmogorovStepper  # noqa: F401
 from .vector_env import KolmogorovVectorEnv  # noqa: F401
+from .slab import SlabKolmogorovSolver  # noqa: F401
+from . import diagnostics, io, wrappers  # noqa: F401
 
 __all__ = ["FlowConfig", "KolmogorovFlow", "KolmogorovFlowParams", "KolmogorovFlowState",
-           "KolmogorovStepper", "KolmogorovVectorEnv"]
+           "KolmogorovStepper", "KolmogorovVectorEnv", "SlabKolmogorovSolver", "diagnostics", "io", "wrappers"]

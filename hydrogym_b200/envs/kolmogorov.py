@@ -68,6 +68,29 @@ class FlowConfig:
     def forcing_function(self, k, x, y):  # K:135-146
         return (np.sin(k * y), np.zeros_like(y))
 
+    def get_observations(self, device=None, dtype=torch.float32):
+        """K:70-87: |velocity| of every snapshot in ``self.vorticity`` (T, N, Mh) at the points
+        ``range(0, n, int(n / (n // obs_size)))`` in x and y -- ``(n // obs_size)**2`` points with stride
+        ``obs_size`` (64 points only when n = obs_size**2; reference quirk kept).  Runs the probe kernel with
+        the snapshots as the batch axis.  Returns (T, points) on the GPU."""
+        if self.vorticity is None:
+            raise ValueError("flow.vorticity is empty: run solve() first")
+        n = self.grid_size[0]
+        divisor = n // self.obs_size
+        if int(n / divisor) * divisor != n:
+            raise ValueError("the reference's point grid needs n to be a multiple of n // obs_size")
+        traj = self.vorticity if isinstance(self.vorticity, torch.Tensor) else torch.from_numpy(np.asarray(self.vorticity))
+        if traj.dim() == 2:
+            traj = traj.unsqueeze(0)
+        rd = torch.float64 if traj.dtype == torch.complex128 else dtype
+        cd = torch.complex128 if rd == torch.float64 else torch.complex64
+        st = KolmogorovStepper(grid_size=self.grid_size, Re=self.Re, k=self.k, num_envs=traj.shape[0], dtype=rd,
+                               device=device, obs_size=divisor, n_inner=1, n_outer=1, domain_x=self.domain_x,
+                               domain_y=self.domain_y)
+        obs, _tke, _nonf = st.reward_obs(traj.to(device=st.device, dtype=cd).unsqueeze(1).contiguous())
+        st.close()
+        return obs
+
 
 @dataclasses.dataclass(frozen=True)
 class KolmogorovFlowParams:

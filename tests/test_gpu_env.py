@@ -100,3 +100,62 @@ def test_solver_surface_and_end_time_guard():
     final, traj = integ.solve(1e-2, flow, (0.0, 1.0), save_n=1, control_field=cf)
     rfinal, rtraj = ref.integrator.solve(1e-2, (0.0, 1.0), 1, control_field=cf)
     assert rel_l2(final.cpu().numpy(), rfinal) < 1e-9
+
+
+def test_wrapper_stack_over_the_cuda_env_matches_oracle():
+    """The reference PPO nesting (run_ppo.py:165-172) over the B200 env: raw quantities from the oracle env, wrapper
+    arithmetic from the NumPy restatement of env_core.py:449-742."""
+    from hydrogym_b200 import KolmogorovFlow
+    from hydrogym_b200 import wrappers as W
+    from oracle import wrappers_oracle as wo
+    B, gamma = 3, 0.99
+    env = KolmogorovFlow(dict(ENV_CFG, dtype="float64", device="cuda:0"), FLOW_CFG)
+    ref = orc.KolmogorovFlow(ENV_CFG, FLOW_CFG, dtype=np.float64)
+    params = env.default_params
+    w = W.NormalizeVecReward(W.NormalizeVecObservation(W.VecEnv(W.ClipAction(W.LogWrapper(env)), num_envs=B)), gamma)
+    assert w.name == "KolmogorovFlow" and w.num_actions == 4          # attribute proxying through 5 wrappers
+    obs, st = w.reset(None, params)
+    robs0, rstate = ref.reset_env()
+    nobs, rno = wo.normalize_obs_reset(np.repeat(robs0[None], B, 0))
+    assert np.abs(obs.cpu().numpy() - nobs).max() < 1e-7  # identical envs: variance 0 -> eps dominates
+    rrw = wo.normalize_reward_reset(B)
+    rlog = dict(episode_returns=np.zeros(B), episode_lengths=np.zeros(B, dtype=np.int64),
+                returned_episode_returns=np.zeros(B), returned_episode_lengths=np.zeros(B, dtype=np.int64),
+                timestep=np.zeros(B, dtype=np.int64))
+    acts = np.array([[-0.25, -0.03, 0.02, 0.01], [1.7, -0.9, 0.1, 0.0], [0.0, 0.0, 0.0, 0.0]])
+    rstates = [dict(rstate) for _ in range(B)]
+    for _ in range(2):
+        obs, st, r, d, info = w.step(None, st, torch.tensor(acts, device="cuda"), params)
+        raw = [ref.step_env(None, rstates[b], np.clip(acts[b], -1.0, 1.0)) for b in range(B)]
+        rstates = [x[1] for x in raw]
+        raw_obs = np.stack([x[0] for x in raw])
+        raw_rew = np.array([float(x[2]) for x in raw])
+        raw_done = np.array([bool(x[3]) for x in raw])
+        nobs, rno = wo.normalize_obs_step(rno, raw_obs)
+        nrew, rrw = wo.normalize_reward_step(rrw, raw_rew, raw_done.astype(np.float64), gamma)
+        linfo, rlog = wo.log_wrapper_step(rlog, raw_rew, raw_done.astype(np.int64))
+        assert np.abs(obs.cpu().numpy() - nobs).max() < 1e-6 * max(1.0, np.abs(nobs).max())
+        assert np.abs(r.cpu().numpy() - nrew).max() < 1e-8 * max(1.0, np.abs(nrew).max())
+        assert np.array_equal(info["timestep"].cpu().numpy(), linfo["timestep"])
+        assert np.allclose(st.env_state.env_state.episode_returns.cpu().numpy(), rlog["episode_returns"], atol=1e-9)
+        assert not bool(d.any())
+
+
+def test_solver_surface_callbacks_observations_and_npy(tmp_path):
+    """Direct-solver surface (docs kolmogorov.md:56-102): solve() with a LogCallback, FlowConfig.get_observations,
+    trajectory .npy round trip -- values against the oracle's solve."""
+    from hydrogym_b200 import KolmogorovFlow, io
+    env = KolmogorovFlow(dict(ENV_CFG, dtype="float64", device="cuda:0"), FLOW_CFG)
+    ref = orc.KolmogorovFlow(ENV_CFG, FLOW_CFG, dtype=np.float64)
+    log = tmp_path / "obs.txt"
+    cb = io.LogCallback(postprocess=lambda f: f.get_observations().mean(dim=1), filename=str(log))
+    final, traj = env.integrator.solve(dt=1e-2, flow=env.flow, t_span=(0.0, 2.0), callbacks=[cb], save_n=1)
+    rfinal, rtraj = ref.integrator.solve(dt=1e-2, t_span=(0.0, 2.0), save_n=1)
+    assert traj.shape == (2, 64, 33) and rel_l2(traj.cpu().numpy(), rtraj) < 1e-9
+    want = np.stack([ref._trajectory_mean_obs(rtraj[t][None]) for t in range(2)])   # n = obs_size^2: same 8x8 points
+    got = env.flow.get_observations()
+    assert got.shape == (2, 64) and np.abs(got.cpu().numpy() - want).max() < 1e-9
+    assert np.allclose(np.loadtxt(log), np.round(want.mean(axis=1), 5), atol=1e-5)
+    io.save_trajectory(str(tmp_path / "traj.npy"), traj)
+    back = io.load_trajectory(str(tmp_path / "traj.npy"), device="cuda")
+    assert torch.equal(back, traj)
