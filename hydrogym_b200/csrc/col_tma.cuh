@@ -127,13 +127,16 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     for (int s = 0; s < STAGES; ++s) {
       const int tile = blockIdx.x + s * gridDim.x;
       if (tile >= ntiles) break;
-      issue(bufs + (3 * s + 0) * kTileEl, &m_adv, bars + 3 * s + 0, tile);
+      int b0, tx0;
+      decode(tile, b0, tx0);
+      if (!(a.dealias && tx0 * TC >= ((MH + 1) * 2) / 3))
+        issue(bufs + (3 * s + 0) * kTileEl, &m_adv, bars + 3 * s + 0, tile);
       if (use_h) issue(bufs + (3 * s + 1) * kTileEl, &m_h, bars + 3 * s + 1, tile);
       issue(bufs + (3 * s + 2) * kTileEl, &m_w, bars + 3 * s + 2, tile);
     }
   }
 
-  uint32_t it = 0;
+  uint32_t it = 0, adv_phase = 0;  // adv_phase bit s: parity of the advection barrier of stage s
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
     const int s = (STAGES == 2) ? (int)(it & 1u) : 0;
     const uint32_t par = (STAGES == 2) ? ((it >> 1) & 1u) : (it & 1u);
@@ -147,6 +150,16 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     const bool special = (tx == 0);  // CTA-uniform
     const int next = tile + STAGES * gridDim.x;  // the tile that will reuse this stage
     const bool has_next = next < ntiles;
+    // 2/3 mask on: the advection term of the columns ky >= km is discarded, so tiles made only of such columns
+    // neither load nor transform it (the row kernel does not write them)
+    constexpr int km = ((MH + 1) * 2) / 3;
+    const bool masked_tile = a.dealias && tx * TC >= km;  // CTA-uniform
+    bool next_masked = false;
+    if (has_next && a.dealias) {
+      int nb2, ntx;
+      decode(next, nb2, ntx);
+      next_masked = ntx * TC >= km;
+    }
     Cx<T>* wnyq = a.wnyq + (size_t)b * N;
     Cx<T>* hnyq = a.hnyq + (size_t)b * N;
     const Cx<T>* G = a.G + (size_t)b * (MH + 1);
@@ -154,12 +167,18 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     if (t == 0) g0 = ldc(G + q);  // forcing + control, row kx = 0 (needed after the FFT)
 
     Cx<T> v[E];
-    mbar_wait(bar + 0, par);
+    if (!masked_tile) {
+      mbar_wait(bar + 0, (adv_phase >> s) & 1u);
+      adv_phase ^= 1u << s;  // one phase per advection tile actually loaded into this stage
 #pragma unroll
-    for (int m = 0; m < E; ++m) v[m] = ldc(buf_adv + (size_t)(t + TPF * m) * TC + c);
-    __syncthreads();  // all rows are in registers before buf_adv becomes the exchange buffer
-    ColEx<T, TC> exA{buf_adv, c};
-    fft_regs<P, -1, T>(v, s_tw, t, exA);
+      for (int m = 0; m < E; ++m) v[m] = ldc(buf_adv + (size_t)(t + TPF * m) * TC + c);
+      __syncthreads();  // all rows are in registers before buf_adv becomes the exchange buffer
+      ColEx<T, TC> exA{buf_adv, c};
+      fft_regs<P, -1, T>(v, s_tw, t, exA);
+    } else {
+#pragma unroll
+      for (int m = 0; m < E; ++m) v[m] = mk<T>((T)0, (T)0);
+    }
 
     if (special) {
       // unpack column 0: A0[kx] = (W[kx] + conj(W[-kx]))/2, An[kx] = (W[kx] - conj(W[-kx]))/(2i)
@@ -176,7 +195,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
       }
       __syncthreads();
     }
-    if (STAGES == 1 && tid == 0 && has_next) {  // single stage: buf_adv is needed first, refill it now
+    if (STAGES == 1 && tid == 0 && has_next && !next_masked) {  // single stage: buf_adv is needed first, refill it now
       fence_proxy_async();
       issue(buf_adv, &m_adv, bar + 0, next);
     }
@@ -195,7 +214,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
         fence_proxy_async();  // make the generic-proxy writes visible to the TMA engine
         __syncthreads();      // ... and buf_h has been consumed: it becomes the exchange buffer
         if (tid == 0) {
-          store_tile(&m_h, buf_adv, b, tx);
+          if (a.store_h) store_tile(&m_h, buf_adv, b, tx);
           store_tile(&m_w, buf_w, b, tx);
           bulk_commit();
         }
@@ -203,7 +222,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
         Cx<T>* wmain = a.wmain + b * plane + q;
         Cx<T>* hmain = a.hmain + b * plane + q;
         rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
-                               [&](int, int kx, Cx<T> h) { stc(hmain + (size_t)kx * MH, h); },
+                               [&](int, int kx, Cx<T> h) { if (a.store_h) stc(hmain + (size_t)kx * MH, h); },
                                [&](int, int kx, Cx<T> wn) {
                                  stc(wmain + (size_t)kx * MH, wn);
                                  stc(buf_w + kx * TC + c, wn);
@@ -221,7 +240,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     if (tid == 0 && has_next) {
       if (TSTORE) bulk_wait_read0();  // the TMA stores have read buf_adv / buf_w
       fence_proxy_async();
-      if (STAGES == 2) issue(buf_adv, &m_adv, bar + 0, next);
+      if (STAGES == 2 && !next_masked) issue(buf_adv, &m_adv, bar + 0, next);
       if (use_h) issue(buf_h, &m_h, bar + 1, next);
       issue(buf_w, &m_w, bar + 2, next);
     }

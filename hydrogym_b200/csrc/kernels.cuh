@@ -40,6 +40,7 @@ template <typename T> struct StageArgs {
   T beta, gdt, munu;   // beta_s, gamma_s*dt, mu_s*nu
   T scale;             // 1/(N*M), folded into the prologue
   int dealias;
+  int store_h;         // 0 in the last sub-stage: the next RK step starts with beta = 0 and never reads h
 };
 
 // exchange policy of the column kernel: TC columns interleaved, conflict-free
@@ -120,7 +121,7 @@ __device__ __forceinline__ void nyquist_column_update(const StageArgs<T>& a, con
     if (a.dealias) h = mk<T>((T)0, (T)0);  // ky = M/2 >= km always
     if (kx == 0) h = h + ldc(G + MH);
     if (use_h) h = h + a.beta * ldc(hnyq + kx);
-    stc(hnyq + kx, h);
+    if (a.store_h) stc(hnyq + kx, h);
     const T p = (T)(kx < N / 2 ? kx : kx - N);
     const T lk = a.munu * (p * p + (T)MH * (T)MH);
     Cx<T> wv = ldc(wnyq + kx);
@@ -249,10 +250,19 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
     const Cx<T>* advx = a.advx + b * plane + q;
     const bool use_h = (a.beta != (T)0);
     Cx<T> v[E];
+    // with the 2/3 mask on, the advection term of every column ky >= km is discarded: such tiles neither read
+    // it nor transform it (the row kernel does not write those columns either)
+    constexpr int km = ((MH + 1) * 2) / 3;
+    const bool masked_tile = a.dealias && (int)blockIdx.x * TC >= km;  // CTA-uniform
+    if (!masked_tile) {
 #pragma unroll
-    for (int m = 0; m < E; ++m) v[m] = ldc(advx + (size_t)(t + TPF * m) * MH);
-    ColEx<T, TC> ex{s_sc, c};
-    fft_regs<P, -1, T>(v, s_tw, t, ex);
+      for (int m = 0; m < E; ++m) v[m] = ldc(advx + (size_t)(t + TPF * m) * MH);
+      ColEx<T, TC> ex{s_sc, c};
+      fft_regs<P, -1, T>(v, s_tw, t, ex);
+    } else {
+#pragma unroll
+      for (int m = 0; m < E; ++m) v[m] = mk<T>((T)0, (T)0);
+    }
 
     if (special) {
       // unpack column 0: A0[kx] = (W[kx] + conj(W[-kx]))/2, An[kx] = (W[kx] - conj(W[-kx]))/(2i)
@@ -272,7 +282,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
     Cx<T> g0 = mk<T>((T)0, (T)0);
     if (t == 0) g0 = ldc(G + q);
     rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
-                           [&](int, int kx, Cx<T> h) { stc(hmain + (size_t)kx * MH, h); },
+                           [&](int, int kx, Cx<T> h) { if (a.store_h) stc(hmain + (size_t)kx * MH, h); },
                            [&](int, int kx, Cx<T> wn) { stc(wmain + (size_t)kx * MH, wn); },
                            [&](int, int kx) { return ldc(hmain + (size_t)kx * MH); },
                            [&](int, int kx) { return ldc(wmain + (size_t)kx * MH); });
@@ -395,9 +405,11 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) row_kernel(StageArgs<T> 
   ex1.sync();
   Cx<T>* o0 = a.advx + b * plane + (size_t)x0 * MH;
   Cx<T>* o1 = o0 + MH;
+  constexpr int km = ((MH + 1) * 2) / 3;
 #pragma unroll
   for (int m = 0; m < E / 2; ++m) {
     const int k = t + TPF * m;
+    if (a.dealias && k >= km) continue;  // masked by the column kernel anyway: never read, so never written
     if (k == 0) {
       const Cx<T> wn = ex1.load(MH);
       stc(o0, mk<T>(v[m].x, wn.x));
