@@ -184,8 +184,8 @@ const SlabOps* find_slab_ops(int dtype, int N) {
 #else
   static const SlabOps f8192 = SlabImpl<float, Plan<8192, 512, 16, 16, 2, 16>, 1, 1>::make();
 #endif
-  static const SlabOps d256 = SlabImpl<double, Plan<256, 32, 8, 4, 8>, 4, 4>::make();
-  static const SlabOps d1024 = SlabImpl<double, Plan<1024, 128, 8, 2, 8, 8>, 1, 1>::make();
+  static const SlabOps d256 = SlabImpl<double, Plan<256, 16, 16, 16>, 8, 8>::make();
+  static const SlabOps d1024 = SlabImpl<double, Plan<1024, 64, 16, 4, 16>, 2, 2>::make();
   const bool f = dtype == KF_F32;
   switch (N) {
     case 256: return f ? &f256 : &d256;
