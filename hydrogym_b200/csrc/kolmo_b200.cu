@@ -295,7 +295,11 @@ int Impl<T, P, TC, GROUPS, CB, RB, TB, ST, TS>::tma_setup(Ctx& c) {
 #define KF_F1024_R2 16
 #endif
 #define KF_CFG_F1024 8, KF_F1024_GROUPS, 1, KF_F1024_RB, KF_F1024_TB
+#ifdef KF_F1024_E32
+#define KF_PLAN_F1024 1024, 32, 32, 32
+#else
 #define KF_PLAN_F1024 1024, 64, 16, KF_F1024_R1, KF_F1024_R2
+#endif
 
 const Ops* find_ops(int dtype, int N) {
   using kf::Plan;
