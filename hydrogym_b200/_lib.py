@@ -21,7 +21,7 @@ SYMBOLS = (
     "kf_slab_create", "kf_slab_destroy", "kf_slab_set_constants", "kf_slab_set_action", "kf_slab_import",
     "kf_slab_export", "kf_slab_exchange_bytes", "kf_slab_col", "kf_slab_row", "kf_slab_obs",
     "kf_slab_launch_count", "kf_slab_workspace_bytes", "kf_energy_spectrum",
-    "kf_slab_p2p_init", "kf_slab_p2p_attach", "kf_slab_p2p_attach_local",
+    "kf_slab_p2p_init", "kf_slab_p2p_attach", "kf_slab_p2p_attach_local", "kf_physical_fields",
 )
 
 
@@ -94,6 +94,8 @@ def load():
     lib.kf_slab_p2p_attach_local.argtypes = [vp, ctypes.POINTER(vp)]
     for name in ("kf_slab_p2p_init", "kf_slab_p2p_attach", "kf_slab_p2p_attach_local"):
         getattr(lib, name).restype = ctypes.c_int
+    lib.kf_physical_fields.argtypes = [vp, vp, vp, ctypes.c_int, vp]
+    lib.kf_physical_fields.restype = ctypes.c_int
     lib.kf_energy_spectrum.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_int, vp]
     lib.kf_energy_spectrum.restype = ctypes.c_int
     _lib = lib

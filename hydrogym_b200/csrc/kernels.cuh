@@ -493,6 +493,38 @@ __global__ void __launch_bounds__(P::TPF* GROUPS) row_obs_kernel(ObsArgs<T> a) {
     for (int i = 0; i < 4; ++i) atomicAdd(acc + i, r[i]);
   }
 }
+// Physical-space fields of one snapshot (diagnostics: compute_energy_dissipation / compute_divergence /
+// compute_real_velocity_point, utils.py:129-172, 213-229, take irfftn of u_hat, v_hat): the c2r y-transform of the
+// x-space fields written out as real arrays out[f][b][x][y], f = 0..3 -> u, v, d(omega)/dx, d(omega)/dy.
+template <typename T, class P, int GROUPS>
+__global__ void __launch_bounds__(P::TPF* GROUPS) row_fields_kernel(ObsArgs<T> a, T* out, int nfields, size_t fstride) {
+  using L2 = typename PairOf<T>::type;
+  constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF, N = M;
+  constexpr int EXN = (int)row_exchange_elems<T, M>();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
+  Cx<L2>* s_ex = reinterpret_cast<Cx<L2>*>(smem_raw) + (size_t)g * EXN;
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
+  RowEx<L2, TPF> ex{s_ex};
+  const int b = blockIdx.y;
+  const int x = blockIdx.x * GROUPS + g;
+  const size_t roff = ((size_t)b * N + x) * MH;
+  for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
+  __syncthreads();
+  Cx<L2> z[E];
+  load_pair_hermitian<L2, P>(z, a.fa + roff, a.fb + roff, t);
+  fft_regs<P, +1, L2>(z, s_tw, t, ex);
+  T* o = out + ((size_t)b * N + x) * M;
+#pragma unroll
+  for (int m = 0; m < E; ++m) {
+    const int y = t + TPF * m;
+    o[y] = z[m].x.lo();
+    if (nfields > 1) o[fstride + y] = z[m].y.lo();
+    if (nfields > 2) o[2 * fstride + y] = z[m].x.hi();
+    if (nfields > 3) o[3 * fstride + y] = z[m].y.hi();
+  }
+}
+
 // mean_tke[b] = mean_j 0.5*(sum((u-U)^2) + sum((v-V)^2))/n^2 ; nonfinite flag
 template <typename T>
 __global__ void tke_finalize_kernel(const double* acc, int B, int nsnap, int N, int M, T* mean_tke, int* nonfinite) {

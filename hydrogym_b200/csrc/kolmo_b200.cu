@@ -61,6 +61,7 @@ struct Ops {
   void (*row)(const struct Ctx&, int nb, cudaStream_t);
   // obs_dev / acc already offset to the chunk's first environment
   void (*obs)(const struct Ctx&, int nb, double* acc, size_t acc_stride, void* obs_dev, double obs_w, cudaStream_t);
+  void (*fields)(const struct Ctx&, int nb, void* out, int nfields, size_t fstride, cudaStream_t);
   void (*finalize)(const struct Ctx&, int nsnap, void* mean_tke, int* nonfinite, cudaStream_t);
   void (*import_)(const struct Ctx&, int nb, const void* user, size_t user_env, cudaStream_t);
   void (*export_)(const struct Ctx&, int nb, void* user, size_t user_env, cudaStream_t);
@@ -113,6 +114,9 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kf::row_kernel<T, P, GROUPS, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem());
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kf::row_fields_kernel<T, P, GROUPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)row_smem());
+    if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(kf::row_obs_kernel<T, P, GROUPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)row_smem());
   }
@@ -150,6 +154,12 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     a.obs_w = (T)obs_w;
     kf::row_obs_kernel<T, P, GROUPS><<<dim3(N / GROUPS, nb), P::TPF * GROUPS, row_smem(), s>>>(a);
   }
+  static void fields(const Ctx& c, int nb, void* out, int nfields, size_t fstride, cudaStream_t s) {
+    kf::ObsArgs<T> a;
+    a.fa = (const C2*)c.fld; a.fb = a.fa + (size_t)c.chunk * c.plane; a.tw = (const C*)c.tw;
+    a.acc = nullptr; a.acc_stride = 0; a.obs = nullptr; a.nobs = 0; a.sx = a.sy = 1; a.obs_w = 0;
+    kf::row_fields_kernel<T, P, GROUPS><<<dim3(N / GROUPS, nb), P::TPF * GROUPS, row_smem(), s>>>(a, (T*)out, nfields, fstride);
+  }
   static void finalize(const Ctx& c, int nsnap, void* mean_tke, int* nonfinite, cudaStream_t s) {
     const int B = c.cfg.B;
     kf::tke_finalize_kernel<T><<<(B + 127) / 128, 128, 0, s>>>(c.acc, B, nsnap, N, N, (T*)mean_tke, nonfinite);
@@ -178,7 +188,7 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     o.elem = sizeof(C);
     o.tc = TC; o.col_threads = P::TPF * TC; o.row_groups = GROUPS; o.row_threads = P::TPF * GROUPS;
     o.col_smem = col_smem(); o.row_smem = row_smem();
-    o.prepare = prepare; o.fill_tw = kf::fill_twiddles<P>; o.tma_setup = tma_setup; o.col_tma = col_tma; o.col = col; o.row = row; o.obs = obs; o.finalize = finalize;
+    o.prepare = prepare; o.fill_tw = kf::fill_twiddles<P>; o.tma_setup = tma_setup; o.col_tma = col_tma; o.col = col; o.row = row; o.obs = obs; o.fields = fields; o.finalize = finalize;
     o.import_ = import_; o.export_ = export_; o.forcing = forcing;
     return o;
   }
@@ -630,6 +640,26 @@ int kf_reward_obs(kf_handle h, const void* trajectory_dev, int n_snap, void* obs
   }
   c.ops->finalize(c, n_snap, mean_tke_dev, nonfinite_dev, s);
   c.launches += 1;
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int kf_physical_fields(kf_handle h, const void* omega_hat_dev, void* out_dev, int nfields, void* stream) {
+  if (!h || !omega_hat_dev || !out_dev) return fail("kf_physical_fields: null argument");
+  if (nfields < 1 || nfields > 4) return fail("kf_physical_fields: nfields must be 1..4 (u, v, d(omega)/dx, d(omega)/dy)");
+  Ctx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t el = c.ops->elem, real = el / 2;
+  const int B = c.cfg.B;
+  const size_t user_env = (size_t)c.N * (c.MH + 1), phys_env = (size_t)c.N * c.N;
+  for (int b0 = 0; b0 < B; b0 += c.chunk) {
+    const int nb = (B - b0 < c.chunk) ? (B - b0) : c.chunk;
+    c.ops->import_(c, nb, (const char*)omega_hat_dev + el * user_env * b0, user_env, s);
+    c.ops->col(c, nb, stage_of(c, 0), kf::kColInit, s);
+    c.ops->fields(c, nb, (char*)out_dev + real * phys_env * b0, nfields, phys_env * B, s);
+    c.launches += 3;
+  }
   KF_CUDA(cudaGetLastError());
   return 0;
 }

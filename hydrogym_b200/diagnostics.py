@@ -55,3 +55,39 @@ def compute_energy_mode(uhat, vhat, kx, ky, n, m):
 def compute_velocity_mode(uhat, vhat, kx, ky, n, m):
     """utils.py:104-121."""
     return torch.sqrt((uhat[..., kx % n, ky % m].abs() ** 2 + vhat[..., kx % n, ky % m].abs() ** 2) / float(n * m) ** 2)
+
+
+def _velocity(omega_hat, Re=1000.0):
+    """(u, v) physical fields (B, N, N) of omega_hat (B, N, Mh) or (N, Mh) through the row-FFT kernels."""
+    from .solver import KolmogorovStepper
+    w = omega_hat[None] if omega_hat.dim() == 2 else omega_hat
+    rd = torch.float32 if w.dtype == torch.complex64 else torch.float64
+    st = KolmogorovStepper(grid_size=(w.shape[1], w.shape[1]), Re=Re, num_envs=w.shape[0], dtype=rd, device=w.device,
+                           n_inner=1, n_outer=1)
+    uv = st.physical_fields(w.contiguous(), 2)
+    st.close()
+    return uv[0], uv[1]
+
+
+def compute_real_velocity_point(omega_hat, x_idx, y_idx):
+    """utils.py:129-142: |velocity| at grid point (x_idx, y_idx)."""
+    u, v = _velocity(omega_hat)
+    out = torch.sqrt(u[:, x_idx, y_idx].abs() ** 2 + v[:, x_idx, y_idx].abs() ** 2)
+    return out[0] if omega_hat.dim() == 2 else out
+
+
+def compute_energy_dissipation(omega_hat, nu):
+    """utils.py:145-172: 2 nu <S_ij S_ij> with the reference's finite differences in INDEX units
+    (jnp.gradient, unit spacing, one-sided at the edges), summed and divided by 4 pi^2."""
+    u, v = _velocity(omega_hat)
+    du_dx, du_dy = torch.gradient(u, dim=(1, 2))
+    dv_dx, dv_dy = torch.gradient(v, dim=(1, 2))
+    eps = (2 * nu * (du_dx ** 2 + dv_dy ** 2 + (du_dy + dv_dx) ** 2)).sum(dim=(1, 2)) / (4 * torch.pi ** 2)
+    return eps[0] if omega_hat.dim() == 2 else eps
+
+
+def compute_divergence(omega_hat):
+    """utils.py:213-229: du/dx + dv/dy with the same index-unit finite differences (not spectrally exact)."""
+    u, v = _velocity(omega_hat)
+    div = torch.gradient(u, dim=1)[0] + torch.gradient(v, dim=2)[0]
+    return div[0] if omega_hat.dim() == 2 else div

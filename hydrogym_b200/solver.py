@@ -160,6 +160,16 @@ class KolmogorovStepper:
                                          _ptr(nonf), self._stream()), "kf_step")
         return final, traj, obs, tke, nonf
 
+    def physical_fields(self, omega_hat, nfields=2):
+        """(nfields, B, N, N) real: u, v[, d(omega)/dx, d(omega)/dy] in physical space (irfftn of the spectral
+        fields of utils.py:53-69 / kolmogorov.py:240-247)."""
+        self._check_state(omega_hat)
+        out = torch.empty((int(nfields), self.B, self.N, self.M), dtype=self.dtype, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.kf_physical_fields(self._h, _ptr(omega_hat), _ptr(out), int(nfields), self._stream()),
+                       "kf_physical_fields")
+        return out
+
     def profile_kernels(self, reps=20):
         """(ms per column-kernel launch, ms per row-kernel launch) on scratch workspace data."""
         a, b = ctypes.c_float(0), ctypes.c_float(0)

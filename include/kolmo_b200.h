@@ -72,6 +72,11 @@ int kf_rk_steps(kf_handle h, void* omega_hat_dev, const void* actions_dev, int n
 int kf_reward_obs(kf_handle h, const void* trajectory_dev, int n_snap, void* obs_dev, void* mean_tke_dev,
                   int* nonfinite_dev, void* stream);
 
+/* Physical-space fields of omega_hat_dev [B][N][M/2+1] (irfftn of the spectral fields of compute_velocity_fft
+ * utils.py:53-69 and of the two vorticity gradients kolmogorov.py:240-247): out_dev [nfields][B][N][M] real,
+ * fields in the order u, v, d(omega)/dx, d(omega)/dy (nfields = 1..4).  Scratches the workspace. */
+int kf_physical_fields(kf_handle h, const void* omega_hat_dev, void* out_dev, int nfields, void* stream);
+
 /* step_env's device work in one call: kf_rollout + kf_reward_obs, the reward/obs
  * reductions running on the snapshots while they are still on chip-side buffers. */
 int kf_step(kf_handle h, void* omega_hat_dev, const void* actions_dev, void* trajectory_dev, void* obs_dev,

@@ -113,6 +113,31 @@ def compute_tke(omega_hat, kx, ky, n):
     return np.sum(avg_tke, axis=(-2, -1))
 
 
+def compute_energy_dissipation(omega_hat, kx, ky, nu, n):
+    """U:145-172 (np.gradient == jnp.gradient: unit spacing, one-sided edges)."""
+    uhat, vhat = compute_velocity_fft(omega_hat, kx, ky)
+    ureal, vreal = _irfft2(uhat), _irfft2(vhat)
+    du_dy = np.gradient(ureal, axis=1)
+    dv_dx = np.gradient(vreal, axis=0)
+    du_dx = np.gradient(ureal, axis=0)
+    dv_dy = np.gradient(vreal, axis=1)
+    avg_epsilon = 2 * nu * ((du_dx) ** 2 + (dv_dy) ** 2 + (du_dy + dv_dx) ** 2)
+    return np.sum(avg_epsilon) / (4 * np.pi ** 2)
+
+
+def compute_divergence(omega_hat, kx, ky):
+    """U:213-229."""
+    uhat, vhat = compute_velocity_fft(omega_hat, kx, ky)
+    ureal, vreal = _irfft2(uhat), _irfft2(vhat)
+    return np.gradient(ureal, axis=0) + np.gradient(vreal, axis=1)
+
+
+def compute_real_velocity_point(uhat, vhat, x_idx, y_idx):
+    """U:129-142."""
+    ureal, vreal = _irfft2(uhat), _irfft2(vhat)
+    return np.sqrt(np.abs(ureal[x_idx, y_idx]) ** 2 + np.abs(vreal[x_idx, y_idx]) ** 2)
+
+
 def compute_energy_mode(uhat, vhat, kx, ky, n, m):
     """U:89-101 -- energy of one mode (kx, ky integer wavenumbers)."""
     return 0.5 * (np.abs(uhat[..., kx % n, ky % m]) ** 2 + np.abs(vhat[..., kx % n, ky % m]) ** 2) / float(n * m) ** 2

@@ -99,3 +99,33 @@ def test_energy_spectrum_statistics_match_oracle_64():
     live = acc_ref > 1e-12 * acc_ref.max()
     assert np.abs(acc[live] - acc_ref[live]).max() < 1e-3 * acc_ref.max()
     assert abs(acc.sum() - acc_ref.sum()) < 1e-4 * acc_ref.sum()
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.complex128, 1e-11), (np.complex64, 2e-5)])
+def test_physical_space_diagnostics_match_oracle(dtype, tol):
+    """compute_energy_dissipation / compute_divergence / compute_real_velocity_point (utils.py:129-172, 213-229)
+    on the physical velocity fields the row-FFT kernels export."""
+    from hydrogym_b200 import KolmogorovStepper, diagnostics
+    N = 128
+    ref = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=np.float64)
+    w = random_states(ref, 2, seed=8).astype(dtype)
+    wt = torch.from_numpy(w).cuda()
+    st = KolmogorovStepper(grid_size=(N, N), Re=100, num_envs=2, device="cuda:0",
+                           dtype=torch.float64 if dtype == np.complex128 else torch.float32)
+    f = st.physical_fields(wt, 4).cpu().numpy()
+    st.close()
+    for b in range(2):
+        w64 = w[b].astype(np.complex128)
+        uh, vh = orc.compute_velocity_fft(w64, ref.kx, ref.ky)
+        p = np.fft.fftfreq(N, 1.0 / N)[:, None]
+        q = np.arange(N // 2 + 1)[None, :]
+        want = [np.fft.irfft2(uh), np.fft.irfft2(vh), np.fft.irfft2(1j * p * w64), np.fft.irfft2(1j * q * w64)]
+        for i in range(4):
+            assert np.abs(f[i, b] - want[i]).max() < tol * np.abs(want[i]).max(), (b, i)
+        eps = float(diagnostics.compute_energy_dissipation(wt[b], 0.01))
+        assert abs(eps - orc.compute_energy_dissipation(w64, ref.kx, ref.ky, 0.01, N)) < 10 * tol * abs(eps)
+        div = diagnostics.compute_divergence(wt[b]).cpu().numpy()
+        wdiv = orc.compute_divergence(w64, ref.kx, ref.ky)
+        assert np.abs(div - wdiv).max() < 10 * tol * max(np.abs(want[0]).max(), np.abs(wdiv).max())
+        pt = float(diagnostics.compute_real_velocity_point(wt[b], 5, 77))
+        assert abs(pt - orc.compute_real_velocity_point(uh, vh, 5, 77)) < tol * max(1.0, pt)
