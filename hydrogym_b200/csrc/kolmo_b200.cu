@@ -304,7 +304,10 @@ int Impl<T, P, TC, GROUPS, CB, RB, TB, ST, TS>::tma_setup(Ctx& c) {
 #ifndef KF_F1024_R2
 #define KF_F1024_R2 16
 #endif
-#define KF_CFG_F1024 8, KF_F1024_GROUPS, 1, KF_F1024_RB, KF_F1024_TB
+#ifndef KF_F1024_TC
+#define KF_F1024_TC 8
+#endif
+#define KF_CFG_F1024 KF_F1024_TC, KF_F1024_GROUPS, 1, KF_F1024_RB, KF_F1024_TB
 #ifdef KF_F1024_E32
 #define KF_PLAN_F1024 1024, 32, 32, 32
 #else
