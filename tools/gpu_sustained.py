@@ -41,4 +41,4 @@ if __name__ == "__main__":
     N, B = int(os.environ.get("KF_N", 256)), int(os.environ.get("KF_B", 256))
     steps = int(os.environ.get("KF_STEPS", 3000))
     for ch in [int(a) for a in sys.argv[1:]] or [0]:
-        run(N, B, torch.float32, chunk=ch, warm=steps // 2, steps=steps)
+        run(N, B, torch.float64 if os.environ.get("KF_DTYPE") == "fp64" else torch.float32, chunk=ch, warm=steps // 2, steps=steps)
