@@ -321,7 +321,7 @@ def run_native(args):
     ms_col, ms_row = st.profile_kernels(reps=20)
     C = N * (N // 2 + 1) * 2 * wbytes            # one spectral field
     chunk = st.chunk
-    lanes = 2 if (B > chunk and args.dtype == "fp32" and os.environ.get("KF_LANES", "") != "1") else 1
+    lanes = st.lanes
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"

@@ -18,6 +18,7 @@ SYMBOLS = (
     "kf_last_error", "kf_create", "kf_destroy", "kf_set_constants", "kf_rollout", "kf_rk_steps",
     "kf_reward_obs", "kf_step", "kf_step_host", "kf_profile_kernels", "kf_launch_count", "kf_workspace_bytes",
     "kf_chunk",
+    "kf_lanes",
     "kf_slab_create", "kf_slab_destroy", "kf_slab_set_constants", "kf_slab_set_action", "kf_slab_import",
     "kf_slab_export", "kf_slab_exchange_bytes", "kf_slab_col", "kf_slab_row", "kf_slab_obs",
     "kf_slab_launch_count", "kf_slab_workspace_bytes", "kf_energy_spectrum",
@@ -63,13 +64,14 @@ def load():
     fp = ctypes.POINTER(ctypes.c_float)
     lib.kf_profile_kernels.argtypes = [vp, ctypes.c_int, fp, fp, vp]
     for name in ("kf_create", "kf_destroy", "kf_set_constants", "kf_rollout", "kf_rk_steps", "kf_reward_obs",
-                 "kf_step", "kf_step_host", "kf_profile_kernels", "kf_chunk"):
+                 "kf_step", "kf_step_host", "kf_profile_kernels", "kf_chunk", "kf_lanes"):
         getattr(lib, name).restype = ctypes.c_int
     lib.kf_launch_count.argtypes = [vp]
     lib.kf_launch_count.restype = ctypes.c_longlong
     lib.kf_workspace_bytes.argtypes = [vp]
     lib.kf_workspace_bytes.restype = ctypes.c_size_t
     lib.kf_chunk.argtypes = [vp]
+    lib.kf_lanes.argtypes = [vp]
     # slab-decomposed single grid
     lib.kf_slab_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(KfConfig), ctypes.c_int, ctypes.c_int]
     lib.kf_slab_destroy.argtypes = [vp]

@@ -705,6 +705,7 @@ long long kf_launch_count(kf_handle h) {
 }
 size_t kf_workspace_bytes(kf_handle h) { return h ? h->c.bytes + (h->c.lane2 ? h->c.lane2->bytes : 0) : 0; }
 int kf_chunk(kf_handle h) { return h ? h->c.chunk : 0; }
+int kf_lanes(kf_handle h) { return h ? (h->c.lane2 ? 2 : 1) : 0; }
 
 }  // extern "C"
 

@@ -110,6 +110,10 @@ class KolmogorovStepper:
     def chunk(self):
         return int(self._lib.kf_chunk(self._h))
 
+    @property
+    def lanes(self):
+        return int(self._lib.kf_lanes(self._h))
+
     # -- device entry points ---------------------------------------------------
     def rk_steps(self, omega_hat, actions, n_steps):
         """Advance ``omega_hat`` (B, N, Mh) IN PLACE by ``n_steps`` RK solver steps."""

@@ -98,6 +98,8 @@ long long kf_launch_count(kf_handle h);
 size_t kf_workspace_bytes(kf_handle h);
 /* Environments per chunk actually used. */
 int kf_chunk(kf_handle h);
+/* Stream lanes the batch is spread over (1 or 2; each lane owns a chunk-sized workspace). */
+int kf_lanes(kf_handle h);
 
 /* Radial kinetic-energy spectrum of omega_hat_dev [B][N][N/2+1] (dtype KF_F32 / KF_F64, no handle needed):
  * spectrum_dev [B][nbins] double, bin = round(|k|), per-mode energy as in compute_energy_mode
