@@ -604,14 +604,18 @@ int kf_create(kf_handle* out, const kf_config* cfg) {
   KF_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
   if (prop.major != 10) return fail("kf_create: this library is built for sm_100a (B200) only");
 
-  // chunking: an explicit chunk is honoured; by default an fp32 batch of >= 64 environments is split into two
-  // chunks so that the two lanes have one each (fp64 measured slower with two lanes: 2.29 -> 2.62 ms per RK step
-  // at 256^2 x 256).  KF_LANES=1 / KF_LANES=2 force one / two lanes (experiments).
+  // chunking: an explicit chunk is honoured; by default an fp32 batch on a grid of at most 512^2 is split into two
+  // chunks, one per lane, when each lane's launches still have >= 256 column tiles.  Sustained measurements
+  // (tools/gpu_sustained.py, % of the HBM roofline, two lanes vs one): 256^2 x 32: 77.6 vs 69.4; 256^2 x 16:
+  // 49.9 vs 54.4 (128 tiles per lane: too few); 512^2 x 16: 58.8 vs 49.1; 512^2 x 32: 59.6 vs 56.4; 1024^2 x 16:
+  // 53.0 vs 55.9 and 1024^2 x 64: 55.0 vs 60.3 (one lane wins); fp64 256^2 x 256: 2.62 vs 2.29 ms (one lane wins).
+  // KF_LANES=1 / KF_LANES=2 force one / two lanes (experiments).
   const char* lanes_env = std::getenv("KF_LANES");
   const bool forced1 = lanes_env && lanes_env[0] == '1', forced2 = lanes_env && lanes_env[0] == '2';
-  const bool two_lanes_wanted = forced2 || (!forced1 && cfg->dtype == KF_F32);
+  const bool two_lanes_wanted = forced2 || (!forced1 && cfg->dtype == KF_F32 && cfg->N <= 512);
   int chunk = (cfg->chunk > 0 && cfg->chunk < cfg->B) ? cfg->chunk : cfg->B;
-  if (cfg->chunk <= 0 && two_lanes_wanted && (cfg->B >= 64 || (forced2 && cfg->B >= 2))) {
+  const bool enough_tiles = (cfg->B / 2) * (cfg->N / 2 / ops->tc) >= 256;
+  if (cfg->chunk <= 0 && two_lanes_wanted && (forced2 ? cfg->B >= 2 : enough_tiles)) {
     chunk = (cfg->B + 1) / 2;
     // L2 time blocking: if both lanes' working sets (7 fields per environment) fit in L2 together, the 4 x-space
     // fields and the advection rows never reach HBM between the two kernels -- less DRAM power, so higher

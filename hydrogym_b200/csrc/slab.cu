@@ -58,6 +58,10 @@ struct SlabCtx {
   void* peer_adv[KF_MAX_PEERS] = {};
   bool ipc_opened[KF_MAX_PEERS] = {};
   bool p2p = false;
+  int sms = 148;
+  // the one-CTA kernel of the packed column runs beside the main column kernel on its own stream
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
@@ -97,6 +101,26 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
     return a;
   }
 
+  // the column / row kernels are persistent: at most one resident wave of CTAs
+  template <class K> static int wave(const SlabCtx& c, K kernel, int threads, size_t smem_bytes, int blocks) {
+    int occ = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, threads, smem_bytes) != cudaSuccess || occ < 1) occ = 1;
+    return blocks < occ * c.sms ? blocks : occ * c.sms;
+  }
+
+  template <int MODE> static void col_kernels(const SlabCtx& c, const kf::SlabArgs<T>& a, cudaStream_t s) {
+    auto main_k = kf::slab_col_kernel<T, P, GROUPS, MODE, false, 1>;
+    const int threads = P::TPF * GROUPS;
+    if (c.rank == 0) {
+      cudaEventRecord(c.ev_fork, s);
+      cudaStreamWaitEvent(c.side, c.ev_fork, 0);
+      kf::slab_col_kernel<T, P, 1, MODE, true, 1><<<1, P::TPF, smem(1), c.side>>>(a);
+      cudaEventRecord(c.ev_join, c.side);
+    }
+    main_k<<<wave(c, main_k, threads, smem(GROUPS), c.Q / GROUPS), threads, smem(GROUPS), s>>>(a);
+    if (c.rank == 0) cudaStreamWaitEvent(s, c.ev_join, 0);
+  }
+
   template <typename V> static void transpose(const V* in, V* out, const kf::TransposeArgs& p, int nz, cudaStream_t s) {
     const dim3 grid((p.Cn + 31) / 32, (p.R + 31) / 32, nz);
     kf::transpose_kernel<V><<<grid, 256, 0, s>>>(in, out, p);
@@ -114,11 +138,9 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
       a.beta = (T)kBeta[stage];
       a.gdt = (T)(kGamma[stage] * c.cfg.dt);                                        // base.py:55
       a.munu = (T)(0.5 * c.cfg.dt * (kAlpha[stage + 1] - kAlpha[stage]) * c.cfg.nu);  // base.py:54
-      if (c.rank == 0) kf::slab_col_kernel<T, P, 1, kf::kSlabStage, true, 1><<<1, P::TPF, smem(1), s>>>(a);
-      kf::slab_col_kernel<T, P, GROUPS, kf::kSlabStage, false, 1><<<Q / GROUPS, P::TPF * GROUPS, smem(GROUPS), s>>>(a);
+      col_kernels<kf::kSlabStage>(c, a, s);
     } else {
-      if (c.rank == 0) kf::slab_col_kernel<T, P, 1, kf::kSlabInit, true, 1><<<1, P::TPF, smem(1), s>>>(a);
-      kf::slab_col_kernel<T, P, GROUPS, kf::kSlabInit, false, 1><<<Q / GROUPS, P::TPF * GROUPS, smem(GROUPS), s>>>(a);
+      col_kernels<kf::kSlabInit>(c, a, s);
     }
     // fak, fbk [Q][N] -> blocks [2][X][Q] per destination rank d (rows x in [d*X, (d+1)*X), array z at + z*XQ):
     // block d of the local send buffer, or slot `rank` of rank d's receive buffer written over NVLink
@@ -135,7 +157,9 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
     a.fbx = a.fax + (size_t)c.X * c.Q;
     for (int d = 0; d < c.P; ++d)
       a.adv_dst[d] = adv_send ? (C*)adv_send + (size_t)d * c.X * c.Q : (C*)c.peer_adv[d] + (size_t)c.rank * c.X * c.Q;
-    kf::slab_row_kernel<T, P, RGROUPS, 1><<<c.X / 2 / RGROUPS, P::TPF * RGROUPS, smem(RGROUPS), s>>>(a);
+    auto k = kf::slab_row_kernel<T, P, RGROUPS, 1>;
+    const int threads = P::TPF * RGROUPS;
+    k<<<wave(c, k, threads, smem(RGROUPS), c.X / 2 / RGROUPS), threads, smem(RGROUPS), s>>>(a);
   }
 
   static void obs(const SlabCtx& c, const void* fld_recv, double* acc, void* obs_dev, double obs_w, cudaStream_t s) {
@@ -210,6 +234,9 @@ void free_all(SlabCtx& c) {
       cudaIpcCloseMemHandle(c.peer_adv[d]);
     }
   }
+  if (c.side) cudaStreamDestroy(c.side);
+  if (c.ev_fork) cudaEventDestroy(c.ev_fork);
+  if (c.ev_join) cudaEventDestroy(c.ev_join);
   void* ptrs[] = {c.wk, c.hk, c.wnyq, c.hnyq, c.G, c.advk, c.fk, c.tw, c.F, c.C, c.own_fld, c.own_adv};
   for (void* p : ptrs)
     if (p) cudaFree(p);
@@ -270,7 +297,14 @@ int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks) {
   c.lgQ = 0;
   while ((1 << c.lgQ) < c.Q) ++c.lgQ;
   const size_t el = ops->elem, qn = (size_t)c.Q * c.N;
+  c.sms = prop.multiProcessorCount;
   int rc = 0;
+  {
+    cudaError_t e = cudaStreamCreateWithFlags(&c.side, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming);
+    if (e != cudaSuccess) rc = fail(std::string("side stream: ") + cudaGetErrorString(e));
+  }
   cudaError_t pe = ops->prepare();
   if (pe != cudaSuccess) rc = fail(std::string("kernel attribute setup: ") + cudaGetErrorString(pe));
   if (!rc) rc = dev_alloc(c, &c.wk, el * qn);

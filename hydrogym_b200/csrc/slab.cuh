@@ -72,6 +72,21 @@ template <typename T, int N, int GROUPS> __host__ __device__ constexpr size_t sl
 
 enum SlabColMode { kSlabStage = 0, kSlabInit = 1 };
 
+// Reload of a value this thread stored earlier in the kernel.  An opaque, ordered load: the compiler can neither
+// forward the stored registers (that is the point -- keeping omega_hat live across the field transforms is what
+// made the 8192-point kernels spill) nor hoist the load above the store.
+__device__ __forceinline__ Cx<float> reload(const Cx<float>* p) {
+  Cx<float> r;
+  asm volatile("ld.global.cg.v2.f32 {%0, %1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ Cx<double> reload(const Cx<double>* p) {
+  Cx<double> r;
+  asm volatile("ld.global.cg.v2.f64 {%0, %1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p) : "memory");
+  return r;
+}
+
+
 // integer wavenumber of row index kx as a real
 template <typename T, int N> __device__ __forceinline__ T wave_of(int kx) { return (T)(kx < N / 2 ? kx : kx - N); }
 
@@ -92,15 +107,19 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
   Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
   RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
   RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
-  const int ql = SPECIAL ? 0 : blockIdx.x * GROUPS + g;
+  for (int i = threadIdx.x; i < N; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
+  __syncthreads();
+
+  // persistent CTAs (the host launches at most one wave): the twiddle table is staged once per CTA
+  const int ncb = SPECIAL ? 1 : a.Q / GROUPS;
+#pragma unroll 1
+  for (int cb = blockIdx.x; cb < ncb; cb += gridDim.x) {
+  const int ql = SPECIAL ? 0 : cb * GROUPS + g;
   const int q = a.q0 + ql;
   const bool live = SPECIAL || q != 0;
   const T tf = (T)t, qf = (T)q;
   Cx<T>* wrow = a.wk + (size_t)ql * N;
   Cx<T>* hrow = a.hk + (size_t)ql * N;
-
-  for (int i = threadIdx.x; i < N; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
-  __syncthreads();
 
   Cx<T> w[E];
   Cx<T> wn[SPECIAL ? E : 1];  // ky = M/2 column (SPECIAL only)
@@ -142,12 +161,11 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
                            [&](int, int kx, Cx<T> wv) { if (live) stc(wrow + kx, wv); },
                            [&](int, int kx) { return ldc(hrow + kx); },
                            [&](int, int kx) { return ldc(wrow + kx); });
-  } else {
+  } else if constexpr (SPECIAL) {
 #pragma unroll
-    for (int m = 0; m < E; ++m) w[m] = ldc(wrow + t + TPF * m);
-    if constexpr (SPECIAL) {
-#pragma unroll
-      for (int m = 0; m < E; ++m) wn[m] = ldc(a.wnyq + t + TPF * m);
+    for (int m = 0; m < E; ++m) {
+      w[m] = ldc(wrow + t + TPF * m);
+      wn[m] = ldc(a.wnyq + t + TPF * m);
     }
   }
 
@@ -170,7 +188,10 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
     for (int m = 0; m < E; ++m) {
       const T p = wave_p<T, P>(tf, m);
       const L2 cf = pair == 0 ? pair_coef<0, T>(p, qf, a.scale) : pair_coef<1, T>(p, qf, a.scale);
-      f[m] = coef_times_iw<T>(cf, w[m]);
+      // the ordinary columns read omega_hat back (L2-hot) instead of holding it across both transforms
+      Cx<T> wv;
+      if constexpr (SPECIAL) wv = w[m]; else wv = reload(wrow + t + TPF * m);
+      f[m] = coef_times_iw<T>(cf, wv);
       if constexpr (SPECIAL) {
         // column 0 <- herm(field[:,0]) + i*herm(field[:,M/2]); herm(c)[kx] = (c[kx] + conj(c[-kx]))/2
         const int mkx = (N - (t + TPF * m)) & (N - 1);
@@ -190,6 +211,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
       for (int m = 0; m < E; ++m) stc(out + t + TPF * m, f[m]);
     }
   }
+  }  // column blocks
 }
 
 // ---------------------------------------------------------------------------
@@ -207,15 +229,20 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_row_kernel(SlabArgs
   Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
   RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
   RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
-  const int xl0 = 2 * (blockIdx.x * GROUPS + g);
   const int Q = a.Q, lgQ = a.lgQ;
 
   for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
   __syncthreads();
 
+  const int nrb = a.X / 2 / GROUPS;  // persistent CTAs, as in the column kernel
+#pragma unroll 1
+  for (int rb = blockIdx.x; rb < nrb; rb += gridDim.x) {
+  const int xl0 = 2 * (rb * GROUPS + g);
   Cx<T> v[E];
 #pragma unroll
-  for (int rr = 0; rr < 2; ++rr) {
+  for (int m = 0; m < E; ++m) v[m] = mk<T>((T)0, (T)0);  // loop-carried below: must not start undefined
+#pragma unroll 1
+  for (int rr = 0; rr < 2; ++rr) {  // not unrolled: one copy of the transform, no loads hoisted across it
     const size_t roff = (size_t)(xl0 + rr) * Q;
     const size_t blk = a.fblk;
     Cx<L2> z[E];
@@ -236,19 +263,23 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_row_kernel(SlabArgs
 #pragma unroll
   for (int m = 0; m < E / 2; ++m) {
     const int k = t + TPF * m;
-    Cx<T>* o0 = a.adv_dst[k >> lgQ] + (size_t)xl0 * Q + (k & (Q - 1));
-    Cx<T>* o1 = o0 + Q;
+    Cx<T> r0, r1;
     if (k == 0) {
       const Cx<T> wn = ex1.load(MH);
-      stc(o0, mk<T>(v[m].x, wn.x));
-      stc(o1, mk<T>(v[m].y, wn.y));
+      r0 = mk<T>(v[m].x, wn.x);
+      r1 = mk<T>(v[m].y, wn.y);
     } else {
       const Cx<T> wm = ex1.load(M - k);
       const Cx<T> s = add_conj(v[m], wm), d = sub_conj(v[m], wm);
-      stc(o0, (T)0.5 * s);
-      stc(o1, mk<T>((T)0.5 * d.y, (T)-0.5 * d.x));
+      r0 = (T)0.5 * s;
+      r1 = mk<T>((T)0.5 * d.y, (T)-0.5 * d.x);
     }
+    Cx<T>* o0 = a.adv_dst[k >> lgQ] + (size_t)xl0 * Q + (k & (Q - 1));
+    stc(o0, r0);
+    stc(o0 + Q, r1);
   }
+  ex1.sync();  // the mirrored reads are done before the next row pair's transform reuses the buffer
+  }  // row blocks
 }
 
 // Reward / observation partial sums of this rank's rows (compute_tke utils.py:175-194,
