@@ -35,6 +35,7 @@ struct SlabOps {
   size_t elem;  // bytes per complex
   cudaError_t (*prepare)();
   void (*fill_tw)(double* re_im);  // transposed twiddle table of the plan (fft.cuh), N complex
+  void (*fill_tw2)(double* re_im);  // the same for the length-N/2 plan of the row kernel, N/2 complex
   void (*col)(const SlabCtx&, int stage, const void* adv_recv, void* fld_send, cudaStream_t);
   void (*row)(const SlabCtx&, const void* fld_recv, void* adv_send, cudaStream_t);
   void (*obs)(const SlabCtx&, const void* fld_recv, double* acc, void* obs, double obs_w, cudaStream_t);
@@ -48,7 +49,7 @@ struct SlabCtx {
   const SlabOps* ops;
   int N, MH, rank, P, Q, X, lgQ;
   void *wk = nullptr, *hk = nullptr, *wnyq = nullptr, *hnyq = nullptr, *G = nullptr, *advk = nullptr, *fk = nullptr;
-  void *tw = nullptr, *F = nullptr, *C = nullptr;
+  void *tw = nullptr, *tw2 = nullptr, *twh = nullptr, *F = nullptr, *C = nullptr;
   size_t bytes = 0;
   long long launches = 0;
   bool have_constants = false;
@@ -64,7 +65,8 @@ struct SlabCtx {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
-template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
+template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> struct SlabImpl {
+  static_assert(PH::L * 2 == P::L, "the row kernel's plan is half the grid size");
   using C = kf::Cx<T>;
   using C2 = kf::Cx<typename kf::PairOf<T>::type>;
   static constexpr int N = P::L, MH = N / 2;
@@ -79,7 +81,7 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
     KF_ATTR((kf::slab_col_kernel<T, P, GROUPS, kf::kSlabInit, false, 1>), smem(GROUPS))
     KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabStage, true, 1>), smem(1))
     KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabInit, true, 1>), smem(1))
-    KF_ATTR((kf::slab_row_kernel<T, P, RGROUPS, 1>), smem(RGROUPS))
+    KF_ATTR((kf::slab_row_half_kernel<T, PH, HGROUPS, 2>), (kf::slab_half_smem_bytes<T, PH::L, HGROUPS>()))
     KF_ATTR((kf::slab_row_obs_kernel<T, P, RGROUPS>), smem(RGROUPS))
 #undef KF_ATTR
     return cudaSuccess;
@@ -92,7 +94,7 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
     a.fak = (C2*)c.fk; a.fbk = a.fak + (size_t)c.Q * N;
     a.fax = nullptr; a.fbx = nullptr; a.fblk = 2 * (size_t)c.X * c.Q;
     for (int d = 0; d < KF_MAX_PEERS; ++d) a.adv_dst[d] = nullptr;
-    a.tw = (const C*)c.tw;
+    a.tw = (const C*)c.tw; a.tw2 = (const C*)c.tw2; a.twh = (const C*)c.twh;
     a.beta = 0; a.gdt = 0; a.munu = 0;
     a.scale = (T)(1.0 / ((double)N * (double)N));
     a.dealias = c.cfg.dealias;
@@ -157,9 +159,10 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
     a.fbx = a.fax + (size_t)c.X * c.Q;
     for (int d = 0; d < c.P; ++d)
       a.adv_dst[d] = adv_send ? (C*)adv_send + (size_t)d * c.X * c.Q : (C*)c.peer_adv[d] + (size_t)c.rank * c.X * c.Q;
-    auto k = kf::slab_row_kernel<T, P, RGROUPS, 1>;
-    const int threads = P::TPF * RGROUPS;
-    k<<<wave(c, k, threads, smem(RGROUPS), c.X / 2 / RGROUPS), threads, smem(RGROUPS), s>>>(a);
+    auto k = kf::slab_row_half_kernel<T, PH, HGROUPS, 2>;
+    const int threads = PH::TPF * HGROUPS;
+    const size_t sm = kf::slab_half_smem_bytes<T, PH::L, HGROUPS>();
+    k<<<wave(c, k, threads, sm, c.X / HGROUPS), threads, sm, s>>>(a);
   }
 
   static void obs(const SlabCtx& c, const void* fld_recv, double* acc, void* obs_dev, double obs_w, cudaStream_t s) {
@@ -192,7 +195,7 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
   static SlabOps make() {
     SlabOps o;
     o.elem = sizeof(C);
-    o.prepare = prepare; o.fill_tw = kf::fill_twiddles<P>; o.col = col; o.row = row; o.obs = obs;
+    o.prepare = prepare; o.fill_tw = kf::fill_twiddles<P>; o.fill_tw2 = kf::fill_twiddles<PH>; o.col = col; o.row = row; o.obs = obs;
     o.import_ = import_; o.export_ = export_; o.forcing = forcing;
     return o;
   }
@@ -200,16 +203,19 @@ template <typename T, class P, int GROUPS, int RGROUPS> struct SlabImpl {
 
 const SlabOps* find_slab_ops(int dtype, int N) {
   using kf::Plan;
-  static const SlabOps f256 = SlabImpl<float, Plan<256, 16, 16, 16>, 8, 8>::make();
-  static const SlabOps f1024 = SlabImpl<float, Plan<1024, 64, 16, 4, 16>, 2, 2>::make();
-  static const SlabOps f4096 = SlabImpl<float, Plan<4096, 256, 16, 16, 16>, 1, 1>::make();
-#ifdef KF_SLAB_E32
-  static const SlabOps f8192 = SlabImpl<float, Plan<8192, 256, 32, 16, 16>, 1, 1>::make();
+  // <dtype, column plan (length N), column groups, obs-row groups, row plan (length N/2), row groups>
+  static const SlabOps f256 = SlabImpl<float, Plan<256, 16, 16, 16>, 8, 8, Plan<128, 8, 16, 8>, 16>::make();
+  static const SlabOps f1024 = SlabImpl<float, Plan<1024, 64, 16, 4, 16>, 2, 2, Plan<512, 32, 8, 8, 8>, 4>::make();
+  static const SlabOps f4096 = SlabImpl<float, Plan<4096, 256, 16, 16, 16>, 1, 1, Plan<2048, 128, 16, 8, 16>, 1>::make();
+#ifdef KF_SLAB_ROW_E8
+  static const SlabOps f8192 =
+      SlabImpl<float, Plan<8192, 512, 16, 16, 2, 16>, 1, 1, Plan<4096, 512, 8, 8, 8, 8>, 1>::make();
 #else
-  static const SlabOps f8192 = SlabImpl<float, Plan<8192, 512, 16, 16, 2, 16>, 1, 1>::make();
+  static const SlabOps f8192 =
+      SlabImpl<float, Plan<8192, 512, 16, 16, 2, 16>, 1, 1, Plan<4096, 256, 16, 16, 16>, 1>::make();
 #endif
-  static const SlabOps d256 = SlabImpl<double, Plan<256, 16, 16, 16>, 8, 8>::make();
-  static const SlabOps d1024 = SlabImpl<double, Plan<1024, 64, 16, 4, 16>, 2, 2>::make();
+  static const SlabOps d256 = SlabImpl<double, Plan<256, 16, 16, 16>, 8, 8, Plan<128, 8, 16, 8>, 16>::make();
+  static const SlabOps d1024 = SlabImpl<double, Plan<1024, 64, 16, 4, 16>, 2, 2, Plan<512, 32, 8, 8, 8>, 4>::make();
   const bool f = dtype == KF_F32;
   switch (N) {
     case 256: return f ? &f256 : &d256;
@@ -237,7 +243,7 @@ void free_all(SlabCtx& c) {
   if (c.side) cudaStreamDestroy(c.side);
   if (c.ev_fork) cudaEventDestroy(c.ev_fork);
   if (c.ev_join) cudaEventDestroy(c.ev_join);
-  void* ptrs[] = {c.wk, c.hk, c.wnyq, c.hnyq, c.G, c.advk, c.fk, c.tw, c.F, c.C, c.own_fld, c.own_adv};
+  void* ptrs[] = {c.wk, c.hk, c.wnyq, c.hnyq, c.G, c.advk, c.fk, c.tw, c.tw2, c.twh, c.F, c.C, c.own_fld, c.own_adv};
   for (void* p : ptrs)
     if (p) cudaFree(p);
 }
@@ -317,15 +323,31 @@ int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks) {
   if (!rc) rc = dev_alloc(c, &c.tw, el * c.N);
   if (!rc) rc = dev_alloc(c, &c.F, el * (c.MH + 1));
   if (!rc) rc = dev_alloc(c, &c.C, el * 4 * (c.MH + 1));
+  if (!rc) rc = dev_alloc(c, &c.tw2, el * c.MH);
+  if (!rc) rc = dev_alloc(c, &c.twh, el * c.MH);
   if (!rc) {
+    // tables are computed in fp64 and rounded once
+    auto upload = [&](void* dst, const std::vector<double>& t64, size_t n) {
+      if (cfg->dtype == KF_F32) {
+        std::vector<float> t32(t64.begin(), t64.begin() + 2 * n);
+        return cudaMemcpy(dst, t32.data(), el * n, cudaMemcpyHostToDevice);
+      }
+      return cudaMemcpy(dst, t64.data(), el * n, cudaMemcpyHostToDevice);
+    };
     std::vector<double> t64(2 * (size_t)c.N);
-    ops->fill_tw(t64.data());  // computed in fp64, rounded once
-    cudaError_t e;
-    if (cfg->dtype == KF_F32) {
-      std::vector<float> t32(t64.begin(), t64.end());
-      e = cudaMemcpy(c.tw, t32.data(), el * c.N, cudaMemcpyHostToDevice);
-    } else {
-      e = cudaMemcpy(c.tw, t64.data(), el * c.N, cudaMemcpyHostToDevice);
+    ops->fill_tw(t64.data());
+    cudaError_t e = upload(c.tw, t64, c.N);
+    if (e == cudaSuccess) {
+      ops->fill_tw2(t64.data());
+      e = upload(c.tw2, t64, c.MH);
+    }
+    if (e == cudaSuccess) {
+      const double kPi = 3.14159265358979323846264338327950288;
+      for (int k = 0; k < c.MH; ++k) {  // exp(-2 pi i k / N): pre / post twiddles of the half-length real transforms
+        t64[2 * k] = std::cos(2.0 * kPi * k / c.N);
+        t64[2 * k + 1] = -std::sin(2.0 * kPi * k / c.N);
+      }
+      e = upload(c.twh, t64, c.MH);
     }
     if (e != cudaSuccess) rc = fail(std::string("twiddle upload: ") + cudaGetErrorString(e));
   }

@@ -42,7 +42,9 @@ template <typename T> struct SlabArgs {
   // [X][Q] -- a slice of the local send buffer (NCCL all-to-all follows) or of rank d's receive buffer mapped
   // over NVLink (peer-to-peer stores straight from this kernel, no separate collective)
   Cx<T>* adv_dst[KF_MAX_PEERS];
-  const Cx<T>* tw;      // [N] exp(-2*pi*i*m/N)
+  const Cx<T>* tw;      // [N] twiddle table of the length-N plan (fft.cuh)
+  const Cx<T>* tw2;     // [N/2] twiddle table of the length-N/2 plan (slab_row_half_kernel)
+  const Cx<T>* twh;     // [N/2] exp(-2*pi*i*k/N)
   T beta, gdt, munu, scale;
   int dealias;
   int q0;               // global packed-column index of local column 0 (rank * Q)
@@ -102,7 +104,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
   constexpr size_t EXN = slab_exchange_elems<N>();
   static_assert(!SPECIAL || GROUPS == 1, "the packed column is one CTA");
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
+  const int g = threadIdx.x / TPF, t0 = threadIdx.x % TPF;
   unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<L2>);
   Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
   RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
@@ -114,6 +116,10 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
   const int ncb = SPECIAL ? 1 : a.Q / GROUPS;
 #pragma unroll 1
   for (int cb = blockIdx.x; cb < ncb; cb += gridDim.x) {
+  // an opaque copy of the thread index per column (and per field pair below): otherwise every address, wavenumber
+  // and exchange offset is loop-invariant and the compiler keeps them all in registers across the transforms
+  int t = t0;
+  asm volatile("" : "+r"(t));
   const int ql = SPECIAL ? 0 : cb * GROUPS + g;
   const int q = a.q0 + ql;
   const bool live = SPECIAL || q != 0;
@@ -130,6 +136,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
 #pragma unroll
     for (int m = 0; m < E; ++m) v[m] = ldc(arow + t + TPF * m);
     fft_regs<P, -1, T>(v, s_tw, t, ex1);
+    if constexpr (!SPECIAL) asm volatile("" : "+r"(t));
     if constexpr (SPECIAL) {
       // unpack: A0[kx] = (W[kx] + conj(W[-kx]))/2 (ky = 0), An[kx] = (W[kx] - conj(W[-kx]))/(2i) (ky = M/2)
 #pragma unroll
@@ -183,6 +190,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
 
 #pragma unroll
   for (int pair = 0; pair < 2; ++pair) {
+    if constexpr (!SPECIAL) asm volatile("" : "+r"(t));
     Cx<L2> f[E];
 #pragma unroll
     for (int m = 0; m < E; ++m) {
@@ -280,6 +288,106 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_row_kernel(SlabArgs
   }
   ex1.sync();  // the mirrored reads are done before the next row pair's transform reuses the buffer
   }  // row blocks
+}
+
+// ---------------------------------------------------------------------------
+// X-layout row kernel, half-length form.  A real row of length M is one complex transform of length H = M/2 of
+// its even / odd samples:
+//     z[n] = x[2n] + i x[2n+1] = IDFT_H( Ev + i Od ),  Ev[k] = X[k] + conj X[H-k],  Od[k] = (X[k] - conj X[H-k]) e^{+2 pi i k / M}
+//     X[k] = (C[k] + conj C[H-k]) / 2 - (i/2) e^{-2 pi i k / M} (C[k] - conj C[H-k]),  C = DFT_H(z)
+// so a group of TPF = H/E threads owns ONE row: two lane-paired inverse transforms ((u, gx) and (v, gy)) and one
+// scalar forward transform of length H.  Against slab_row_kernel (two rows through length-M transforms) the
+// register file holds half as much per CTA, so two CTAs fit on an SM and one's loads overlap the other's
+// butterflies.  PH is the plan of length H; a.tw2 its twiddle table, a.twh[k] = e^{-2 pi i k / M}, k < H.
+// grid: persistent, row blocks of GROUPS rows.
+// ---------------------------------------------------------------------------
+template <typename T, int H, int GROUPS> __host__ __device__ constexpr size_t slab_half_smem_bytes() {
+  return sizeof(Cx<typename PairOf<T>::type>) * GROUPS * slab_exchange_elems<H>() + sizeof(Cx<T>) * (size_t)H;
+}
+
+template <typename T, class PH, int GROUPS, int MINB>
+__global__ void __launch_bounds__(PH::TPF* GROUPS, MINB) slab_row_half_kernel(SlabArgs<T> a) {
+  using L2 = typename PairOf<T>::type;
+  constexpr int H = PH::L, E = PH::E, TPF = PH::TPF;
+  constexpr size_t EXN = slab_exchange_elems<H>();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
+  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<L2>);
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
+  RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
+  RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
+  const int Q = a.Q, lgQ = a.lgQ;
+  const unsigned blk = (unsigned)a.fblk;  // element offsets of a slab fit 32 bits (N * N complex at most)
+
+  for (int i = threadIdx.x; i < H; i += TPF * GROUPS) s_tw[i] = ldc(a.tw2 + i);
+  __syncthreads();
+
+  const int nrb = a.X / GROUPS;
+#pragma unroll 1
+  for (int rb = blockIdx.x; rb < nrb; rb += gridDim.x) {
+    const int xl = rb * GROUPS + g;
+    const size_t roff = (size_t)xl * Q;
+    T acc_e[E], acc_o[E];  // sum over the two lane pairs of (velocity * gradient) at samples 2n, 2n+1
+#pragma unroll
+    for (int m = 0; m < E; ++m) acc_e[m] = (T)0, acc_o[m] = (T)0;
+#pragma unroll 1
+    for (int pair = 0; pair < 2; ++pair) {
+      const Cx<L2>* F = (pair == 0 ? a.fax : a.fbx) + roff;
+      // nothing below depends on `pair` or `rb` except through F: an opaque copy of the thread index keeps the
+      // compiler from hoisting the 2 E element offsets, the twiddle addresses and the exchange addresses out of
+      // the loops (they would occupy the registers the transform needs)
+      int tp = t;
+      asm volatile("" : "+r"(tp));
+      auto at = [&](int k) { return (unsigned)(k >> lgQ) * blk + (unsigned)(k & (Q - 1)); };
+      Cx<L2> z[E];
+#pragma unroll
+      for (int m = 0; m < E; ++m) {
+        const int k = tp + TPF * m;
+        const Cx<L2> xk = ldc(F + at(k));
+        const Cx<L2> xm = ldc(F + at(k == 0 ? 0 : H - k));
+        const Cx<T> th = ldc(a.twh + k);  // (cos, -sin) of 2 pi k / M
+        const Cx<L2> ev = add_conj(xk, xm), d = sub_conj(xk, xm);
+        // od = d * conj(th);  z = ev + i * od
+        const L2 c = bc<L2>(th.x), sn = bc<L2>(-th.y);
+        const Cx<L2> od = mk<L2>(d.x * c - d.y * sn, d.x * sn + d.y * c);
+        const Cx<L2> zk = mk<L2>(ev.x - od.y, ev.y + od.x);
+        // packed entry 0 holds the two real values X[0], X[H]:  z[0] = (X0 + XH) + i (X0 - XH)
+        const Cx<L2> z0 = mk<L2>(xk.x + xk.y, xk.x - xk.y);
+        z[m] = (k == 0) ? z0 : zk;
+      }
+      fft_regs<PH, +1, L2>(z, s_tw, tp, ex2);
+#pragma unroll
+      for (int m = 0; m < E; ++m) {
+        acc_e[m] = fmaL(z[m].x.lo(), z[m].x.hi(), acc_e[m]);  // kolmogorov.py:249
+        acc_o[m] = fmaL(z[m].y.lo(), z[m].y.hi(), acc_o[m]);
+      }
+    }
+    Cx<T> v[E];
+#pragma unroll
+    for (int m = 0; m < E; ++m) v[m] = mk<T>(-acc_e[m], -acc_o[m]);
+    int tq = t;
+    asm volatile("" : "+r"(tq));
+    fft_regs<PH, -1, T>(v, s_tw, tq, ex1);
+#pragma unroll
+    for (int m = 0; m < E; ++m) ex1.store(tq + TPF * m, v[m]);
+    ex1.sync();
+#pragma unroll
+    for (int m = 0; m < E; ++m) {
+      const int k = tq + TPF * m;
+      Cx<T> r;
+      if (k == 0) {
+        r = mk<T>(v[m].x + v[m].y, v[m].x - v[m].y);  // (X[0], X[H]) packed
+      } else {
+        const Cx<T> cm = ex1.load(H - k);
+        const Cx<T> th = ldc(a.twh + k);
+        const Cx<T> sm = add_conj(v[m], cm), d = sub_conj(v[m], cm);
+        const T pa = th.x * d.x - th.y * d.y, pb = th.x * d.y + th.y * d.x;  // th * d
+        r = mk<T>((T)0.5 * (sm.x + pb), (T)0.5 * (sm.y - pa));
+      }
+      stc(a.adv_dst[k >> lgQ] + (size_t)xl * Q + (k & (Q - 1)), r);
+    }
+    ex1.sync();
+  }
 }
 
 // Reward / observation partial sums of this rank's rows (compute_tke utils.py:175-194,
