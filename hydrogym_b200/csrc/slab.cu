@@ -72,17 +72,20 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
   static constexpr int N = P::L, MH = N / 2;
   static size_t smem(int groups) { return sizeof(C2) * groups * kf::slab_exchange_elems<N>() + sizeof(C) * (size_t)N; }
 
+  static size_t smem_scalar() { return kf::slab_scalar_smem_bytes<T, N, GROUPS>(); }
+  static size_t smem_obs() { return sizeof(C) * (RGROUPS * kf::slab_exchange_elems<N>() + (size_t)N); }
+
   static cudaError_t prepare() {
     cudaError_t e;
 #define KF_ATTR(k, bytes)                                                                              \
   e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes));              \
   if (e != cudaSuccess) return e;
-    KF_ATTR((kf::slab_col_kernel<T, P, GROUPS, kf::kSlabStage, false, 1>), smem(GROUPS))
-    KF_ATTR((kf::slab_col_kernel<T, P, GROUPS, kf::kSlabInit, false, 1>), smem(GROUPS))
+    KF_ATTR((kf::slab_col_scalar_kernel<T, P, GROUPS, kf::kSlabStage, 2>), smem_scalar())
+    KF_ATTR((kf::slab_col_scalar_kernel<T, P, GROUPS, kf::kSlabInit, 2>), smem_scalar())
     KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabStage, true, 1>), smem(1))
     KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabInit, true, 1>), smem(1))
     KF_ATTR((kf::slab_row_half_kernel<T, PH, HGROUPS, 2>), (kf::slab_half_smem_bytes<T, PH::L, HGROUPS>()))
-    KF_ATTR((kf::slab_row_obs_kernel<T, P, RGROUPS>), smem(RGROUPS))
+    KF_ATTR((kf::slab_row_obs_kernel<T, P, RGROUPS>), smem_obs())
 #undef KF_ATTR
     return cudaSuccess;
   }
@@ -91,8 +94,8 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
     kf::SlabArgs<T> a;
     a.wk = (C*)c.wk; a.hk = (C*)c.hk; a.wnyq = (C*)c.wnyq; a.hnyq = (C*)c.hnyq;
     a.G = (const C*)c.G; a.advk = (const C*)c.advk;
-    a.fak = (C2*)c.fk; a.fbk = a.fak + (size_t)c.Q * N;
-    a.fax = nullptr; a.fbx = nullptr; a.fblk = 2 * (size_t)c.X * c.Q;
+    a.fk = (C*)c.fk;
+    a.fx = nullptr; a.fblk = 4 * (size_t)c.X * c.Q;
     for (int d = 0; d < KF_MAX_PEERS; ++d) a.adv_dst[d] = nullptr;
     a.tw = (const C*)c.tw; a.tw2 = (const C*)c.tw2; a.twh = (const C*)c.twh;
     a.beta = 0; a.gdt = 0; a.munu = 0;
@@ -111,7 +114,7 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
   }
 
   template <int MODE> static void col_kernels(const SlabCtx& c, const kf::SlabArgs<T>& a, cudaStream_t s) {
-    auto main_k = kf::slab_col_kernel<T, P, GROUPS, MODE, false, 1>;
+    auto main_k = kf::slab_col_scalar_kernel<T, P, GROUPS, MODE, 2>;
     const int threads = P::TPF * GROUPS;
     if (c.rank == 0) {
       cudaEventRecord(c.ev_fork, s);
@@ -119,12 +122,15 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
       kf::slab_col_kernel<T, P, 1, MODE, true, 1><<<1, P::TPF, smem(1), c.side>>>(a);
       cudaEventRecord(c.ev_join, c.side);
     }
-    main_k<<<wave(c, main_k, threads, smem(GROUPS), c.Q / GROUPS), threads, smem(GROUPS), s>>>(a);
+    main_k<<<wave(c, main_k, threads, smem_scalar(), c.Q / GROUPS), threads, smem_scalar(), s>>>(a);
     if (c.rank == 0) cudaStreamWaitEvent(s, c.ev_join, 0);
   }
 
-  template <typename V> static void transpose(const V* in, V* out, const kf::TransposeArgs& p, int nz, cudaStream_t s) {
+  template <typename V> static void transpose(const V* in, V* out, kf::TransposeArgs p, int nz, cudaStream_t s) {
     const dim3 grid((p.Cn + 31) / 32, (p.R + 31) / 32, nz);
+    p.in_lg = p.out_lg = 0;  // rows per block are N, Q or X: powers of two (kf_slab_create checks nranks)
+    while ((1 << p.in_lg) < p.in_rpb) ++p.in_lg;
+    while ((1 << p.out_lg) < p.out_rpb) ++p.out_lg;
     kf::transpose_kernel<V><<<grid, 256, 0, s>>>(in, out, p);
   }
 
@@ -144,19 +150,18 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
     } else {
       col_kernels<kf::kSlabInit>(c, a, s);
     }
-    // fak, fbk [Q][N] -> blocks [2][X][Q] per destination rank d (rows x in [d*X, (d+1)*X), array z at + z*XQ):
-    // block d of the local send buffer, or slot `rank` of rank d's receive buffer written over NVLink
-    kf::TransposeArgs p{Q, N, Q, X, 0, (size_t)N, (size_t)Q * N, 2 * (size_t)X * Q, (size_t)Q, (size_t)X * Q, {}};
+    // field planes [4][Q][N] -> blocks [4][X][Q] per destination rank d (rows x in [d*X, (d+1)*X), plane z at
+    // + z*XQ): block d of the local send buffer, or slot `rank` of rank d's receive buffer written over NVLink
+    kf::TransposeArgs p{Q, N, Q, X, 0, (size_t)N, (size_t)Q * N, 4 * (size_t)X * Q, (size_t)Q, (size_t)X * Q, {}};
     for (int d = 0; d < c.P; ++d)
-      p.out_tab[d] = fld_send ? (void*)((C2*)fld_send + (size_t)d * 2 * X * Q)
-                              : (void*)((C2*)c.peer_fld[d] + (size_t)c.rank * 2 * X * Q);
-    transpose<C2>((const C2*)c.fk, (C2*)nullptr, p, 2, s);
+      p.out_tab[d] = fld_send ? (void*)((C*)fld_send + (size_t)d * 4 * X * Q)
+                              : (void*)((C*)c.peer_fld[d] + (size_t)c.rank * 4 * X * Q);
+    transpose<C>((const C*)c.fk, (C*)nullptr, p, 4, s);
   }
 
   static void row(const SlabCtx& c, const void* fld_recv, void* adv_send, cudaStream_t s) {
     kf::SlabArgs<T> a = args(c);
-    a.fax = (const C2*)(fld_recv ? fld_recv : c.own_fld);
-    a.fbx = a.fax + (size_t)c.X * c.Q;
+    a.fx = (const C*)(fld_recv ? fld_recv : c.own_fld);
     for (int d = 0; d < c.P; ++d)
       a.adv_dst[d] = adv_send ? (C*)adv_send + (size_t)d * c.X * c.Q : (C*)c.peer_adv[d] + (size_t)c.rank * c.X * c.Q;
     auto k = kf::slab_row_half_kernel<T, PH, HGROUPS, 2>;
@@ -167,10 +172,9 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
 
   static void obs(const SlabCtx& c, const void* fld_recv, double* acc, void* obs_dev, double obs_w, cudaStream_t s) {
     kf::SlabArgs<T> a = args(c);
-    a.fax = (const C2*)(fld_recv ? fld_recv : c.own_fld);
-    a.fbx = a.fax + (size_t)c.X * c.Q;
+    a.fx = (const C*)(fld_recv ? fld_recv : c.own_fld);
     const int st = N / c.cfg.obs_size;
-    kf::slab_row_obs_kernel<T, P, RGROUPS><<<c.X / RGROUPS, P::TPF * RGROUPS, smem(RGROUPS), s>>>(
+    kf::slab_row_obs_kernel<T, P, RGROUPS><<<c.X / RGROUPS, P::TPF * RGROUPS, smem_obs(), s>>>(
         a, acc, (T*)obs_dev, c.cfg.obs_size, st, st, (T)obs_w);
   }
 

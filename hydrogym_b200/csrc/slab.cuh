@@ -32,12 +32,10 @@ template <typename T> struct SlabArgs {
   Cx<T>* hnyq;          // [N]
   const Cx<T>* G;       // [M/2+1] forcing + control row (kx = 0)
   const Cx<T>* advk;    // [Q][N] packed x-space advection, transposed
-  Cx<L2>* fak;          // [Q][N] lanes (u_hat, gx_hat)
-  Cx<L2>* fbk;          // [Q][N] lanes (v_hat, gy_hat)
-  // X layout, blocked: element (xl, k) of a half-row at (k / Q) * blk + xl * Q + k % Q
-  const Cx<L2>* fax;    // fields received from the peers
-  const Cx<L2>* fbx;
-  size_t fblk;          // block stride of fax / fbx (2*X*Q: fa and fb of one peer are adjacent)
+  Cx<T>* fk;            // [4][Q][N] planes u_hat, gx_hat, v_hat, gy_hat (x-space after the column kernel)
+  // X layout, blocked: element (xl, k) of a half-row of plane f at (k / Q) * fblk + f * X*Q + xl * Q + k % Q
+  const Cx<T>* fx;      // fields received from the peers
+  size_t fblk;          // block stride of fx (4*X*Q: the four planes of one peer are adjacent)
   // advection rows leave in blocks of Q columns: block d (the columns rank d owns) starts at adv_dst[d] and is
   // [X][Q] -- a slice of the local send buffer (NCCL all-to-all follows) or of rank d's receive buffer mapped
   // over NVLink (peer-to-peer stores straight from this kernel, no separate collective)
@@ -213,81 +211,99 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
       }
     }
     fft_regs<P, +1, L2>(f, s_tw, t, ex2);
-    Cx<L2>* out = (pair == 0 ? a.fak : a.fbk) + (size_t)ql * N;
+    Cx<T>* o0 = a.fk + ((size_t)(2 * pair) * a.Q + ql) * N;  // planes 2 pair (lane 0) and 2 pair + 1 (lane 1)
+    Cx<T>* o1 = o0 + (size_t)a.Q * N;
     if (live) {
 #pragma unroll
-      for (int m = 0; m < E; ++m) stc(out + t + TPF * m, f[m]);
+      for (int m = 0; m < E; ++m) {
+        stc(o0 + t + TPF * m, mk<T>(f[m].x.lo(), f[m].y.lo()));
+        stc(o1 + t + TPF * m, mk<T>(f[m].x.hi(), f[m].y.hi()));
+      }
     }
   }
   }  // column blocks
 }
 
 // ---------------------------------------------------------------------------
-// X-layout row kernel: the arithmetic of row_kernel (kernels.cuh) on the blocked slab layout.  A group of
-// TPF threads owns the local rows (xl0, xl0 + 1); grid = X / 2 / GROUPS.
+// K-layout column kernel of the ordinary columns, scalar lanes.  The same arithmetic as slab_col_kernel (which now
+// only serves the packed column), but every transform is a scalar one: 32 data registers per thread instead of
+// 64, so the kernel fits 64 registers and TWO 512-thread CTAs share an SM at 8192 points -- one CTA's loads
+// overlap the other's butterflies, which is what the lane-paired form (one CTA per SM, all warps in the same
+// phase) could not do.  The four fields are four transforms written to four planes.  Twiddles come from global
+// memory through L1 (the table is shared by both CTAs; the streaming operands bypass or leave L1 early).
+// grid: persistent over the Q local columns (global column 0 is computed but not stored).
 // ---------------------------------------------------------------------------
-template <typename T, class P, int GROUPS, int MINB>
-__global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_row_kernel(SlabArgs<T> a) {
-  using L2 = typename PairOf<T>::type;
-  constexpr int M = P::L, MH = M / 2, E = P::E, TPF = P::TPF;
-  constexpr size_t EXN = slab_exchange_elems<M>();
+template <typename T, int N, int GROUPS> __host__ __device__ constexpr size_t slab_scalar_smem_bytes() {
+  return sizeof(Cx<T>) * GROUPS * slab_exchange_elems<N>();
+}
+__device__ __forceinline__ Cx<float> ld_stream(const Cx<float>* p) {
+  const float2 v = __ldcs(reinterpret_cast<const float2*>(p));
+  return mk<float>(v.x, v.y);
+}
+__device__ __forceinline__ Cx<double> ld_stream(const Cx<double>* p) {
+  const double2 v = __ldcs(reinterpret_cast<const double2*>(p));
+  return mk<double>(v.x, v.y);
+}
+
+template <typename T, class P, int GROUPS, int MODE, int MINB>
+__global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_scalar_kernel(SlabArgs<T> a) {
+  constexpr int N = P::L, E = P::E, TPF = P::TPF;
+  constexpr size_t EXN = slab_exchange_elems<N>();
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
-  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<L2>);
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
-  RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
-  RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
-  const int Q = a.Q, lgQ = a.lgQ;
+  const int g = threadIdx.x / TPF, t0 = threadIdx.x % TPF;
+  RowEx<T, TPF> ex{reinterpret_cast<Cx<T>*>(smem_raw) + (size_t)g * EXN};
+  const Cx<T>* __restrict__ tw = a.tw;
 
-  for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
-  __syncthreads();
+  const int ncb = a.Q / GROUPS;
+#pragma unroll 1
+  for (int cb = blockIdx.x; cb < ncb; cb += gridDim.x) {
+    int t = t0;
+    asm volatile("" : "+r"(t));  // see slab_col_kernel
+    const int ql = cb * GROUPS + g;
+    const int q = a.q0 + ql;
+    const bool live = q != 0;
+    const T qf = (T)q;
+    Cx<T>* wrow = a.wk + (size_t)ql * N;
+    Cx<T>* hrow = a.hk + (size_t)ql * N;
 
-  const int nrb = a.X / 2 / GROUPS;  // persistent CTAs, as in the column kernel
-#pragma unroll 1
-  for (int rb = blockIdx.x; rb < nrb; rb += gridDim.x) {
-  const int xl0 = 2 * (rb * GROUPS + g);
-  Cx<T> v[E];
+    if constexpr (MODE == kSlabStage) {
+      const bool use_h = (a.beta != (T)0);
+      Cx<T> v[E], w[E];
+      const Cx<T>* arow = a.advk + (size_t)ql * N;
 #pragma unroll
-  for (int m = 0; m < E; ++m) v[m] = mk<T>((T)0, (T)0);  // loop-carried below: must not start undefined
+      for (int m = 0; m < E; ++m) v[m] = ld_stream(arow + t + TPF * m);
+      fft_regs<P, -1, T>(v, tw, t, ex);
+      asm volatile("" : "+r"(t));
+      Cx<T> g0 = mk<T>((T)0, (T)0);
+      if (t == 0) g0 = ldc(a.G + q);
+      rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
+                             [&](int, int kx, Cx<T> h) { if (live) stc(hrow + kx, h); },
+                             [&](int, int kx, Cx<T> wv) { if (live) stc(wrow + kx, wv); },
+                             [&](int, int kx) { return ld_stream(hrow + kx); },
+                             [&](int, int kx) { return ld_stream(wrow + kx); });
+    }
+
 #pragma unroll 1
-  for (int rr = 0; rr < 2; ++rr) {  // not unrolled: one copy of the transform, no loads hoisted across it
-    const size_t roff = (size_t)(xl0 + rr) * Q;
-    const size_t blk = a.fblk;
-    Cx<L2> z[E];
-    load_pair_hermitian_at<L2, P>(z, a.fax + roff, a.fbx + roff, t,
-                                  [&](int k) { return (size_t)(k >> lgQ) * blk + (k & (Q - 1)); });
-    fft_regs<P, +1, L2>(z, s_tw, t, ex2);
+    for (int fld = 0; fld < 4; ++fld) {  // u_hat, gx_hat, v_hat, gy_hat = c * (i omega_hat), kernels.cuh pair_coef
+      asm volatile("" : "+r"(t));
+      const T tf = (T)t;
+      Cx<T> f[E];
 #pragma unroll
-    for (int m = 0; m < E; ++m) {
-      const T adv = -(z[m].x.lo() * z[m].x.hi() + z[m].y.lo() * z[m].y.hi());  // kolmogorov.py:249
-      if (rr == 0) v[m].x = adv; else v[m].y = adv;
+      for (int m = 0; m < E; ++m) {
+        const Cx<T> wv = reload(wrow + t + TPF * m);  // L2-hot: this thread stored it above
+        const T p = wave_p<T, P>(tf, m);
+        const T sp = p * a.scale, sq = qf * a.scale, ik2 = inv_k2<T>(p, qf);
+        const T c = fld == 0 ? sq * ik2 : fld == 1 ? sp : fld == 2 ? -(sp * ik2) : sq;
+        f[m] = mk<T>(c * -wv.y, c * wv.x);
+      }
+      fft_regs<P, +1, T>(f, tw, t, ex);
+      Cx<T>* out = a.fk + ((size_t)fld * a.Q + ql) * N;
+      if (live) {
+#pragma unroll
+        for (int m = 0; m < E; ++m) stc(out + t + TPF * m, f[m]);
+      }
     }
   }
-
-  fft_regs<P, -1, T>(v, s_tw, t, ex1);
-#pragma unroll
-  for (int m = 0; m < E; ++m) ex1.store(t + TPF * m, v[m]);
-  ex1.sync();
-#pragma unroll
-  for (int m = 0; m < E / 2; ++m) {
-    const int k = t + TPF * m;
-    Cx<T> r0, r1;
-    if (k == 0) {
-      const Cx<T> wn = ex1.load(MH);
-      r0 = mk<T>(v[m].x, wn.x);
-      r1 = mk<T>(v[m].y, wn.y);
-    } else {
-      const Cx<T> wm = ex1.load(M - k);
-      const Cx<T> s = add_conj(v[m], wm), d = sub_conj(v[m], wm);
-      r0 = (T)0.5 * s;
-      r1 = mk<T>((T)0.5 * d.y, (T)-0.5 * d.x);
-    }
-    Cx<T>* o0 = a.adv_dst[k >> lgQ] + (size_t)xl0 * Q + (k & (Q - 1));
-    stc(o0, r0);
-    stc(o0 + Q, r1);
-  }
-  ex1.sync();  // the mirrored reads are done before the next row pair's transform reuses the buffer
-  }  // row blocks
 }
 
 // ---------------------------------------------------------------------------
@@ -332,7 +348,13 @@ __global__ void __launch_bounds__(PH::TPF* GROUPS, MINB) slab_row_half_kernel(Sl
     for (int m = 0; m < E; ++m) acc_e[m] = (T)0, acc_o[m] = (T)0;
 #pragma unroll 1
     for (int pair = 0; pair < 2; ++pair) {
-      const Cx<L2>* F = (pair == 0 ? a.fax : a.fbx) + roff;
+      // planes (u, gx) for pair 0, (v, gy) for pair 1, packed into the two lanes as they are loaded
+      const Cx<T>* F0 = a.fx + (size_t)(2 * pair) * a.X * Q + roff;
+      const Cx<T>* F1 = F0 + (size_t)a.X * Q;
+      auto ldp = [&](unsigned off) {
+        const Cx<T> p0 = ldc(F0 + off), p1 = ldc(F1 + off);
+        return mk<L2>(L2(p0.x, p1.x), L2(p0.y, p1.y));
+      };
       // nothing below depends on `pair` or `rb` except through F: an opaque copy of the thread index keeps the
       // compiler from hoisting the 2 E element offsets, the twiddle addresses and the exchange addresses out of
       // the loops (they would occupy the registers the transform needs)
@@ -343,8 +365,8 @@ __global__ void __launch_bounds__(PH::TPF* GROUPS, MINB) slab_row_half_kernel(Sl
 #pragma unroll
       for (int m = 0; m < E; ++m) {
         const int k = tp + TPF * m;
-        const Cx<L2> xk = ldc(F + at(k));
-        const Cx<L2> xm = ldc(F + at(k == 0 ? 0 : H - k));
+        const Cx<L2> xk = ldp(at(k));
+        const Cx<L2> xm = ldp(at(k == 0 ? 0 : H - k));
         const Cx<T> th = ldc(a.twh + k);  // (cos, -sin) of 2 pi k / M
         const Cx<L2> ev = add_conj(xk, xm), d = sub_conj(xk, xm);
         // od = d * conj(th);  z = ev + i * od
@@ -397,14 +419,12 @@ __global__ void __launch_bounds__(PH::TPF* GROUPS, MINB) slab_row_half_kernel(Sl
 template <typename T, class P, int GROUPS>
 __global__ void __launch_bounds__(P::TPF* GROUPS) slab_row_obs_kernel(SlabArgs<T> a, double* acc, T* obs, int nobs,
                                                                       int sx, int sy, T obs_w) {
-  using L2 = typename PairOf<T>::type;
   constexpr int M = P::L, E = P::E, TPF = P::TPF;
   constexpr size_t EXN = slab_exchange_elems<M>();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
-  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<L2>);
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
-  RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
+  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw) + (size_t)GROUPS * EXN;
+  RowEx<T, TPF> ex{reinterpret_cast<Cx<T>*>(smem_raw) + (size_t)g * EXN};
   const int xl = blockIdx.x * GROUPS + g;
   const int x = a.x0 + xl;
   const int Q = a.Q, lgQ = a.lgQ;
@@ -413,15 +433,16 @@ __global__ void __launch_bounds__(P::TPF* GROUPS) slab_row_obs_kernel(SlabArgs<T
   __syncthreads();
 
   const size_t roff = (size_t)xl * Q, blk = a.fblk;
-  Cx<L2> z[E];
-  load_pair_hermitian_at<L2, P>(z, a.fax + roff, a.fbx + roff, t,
-                                [&](int k) { return (size_t)(k >> lgQ) * blk + (k & (Q - 1)); });
-  fft_regs<P, +1, L2>(z, s_tw, t, ex2);
+  // one scalar transform of u_hat + i v_hat (planes 0 and 2): real part u, imaginary part v
+  Cx<T> z[E];
+  load_pair_hermitian_at<T, P>(z, a.fx + roff, a.fx + 2 * (size_t)a.X * Q + roff, t,
+                               [&](int k) { return (size_t)(k >> lgQ) * blk + (k & (Q - 1)); });
+  fft_regs<P, +1, T>(z, s_tw, t, ex);
 
   T su = 0, sv = 0, suu = 0, svv = 0;
 #pragma unroll
   for (int m = 0; m < E; ++m) {
-    const T u = z[m].x.lo(), vv = z[m].y.lo();
+    const T u = z[m].x, vv = z[m].y;
     su += u; sv += vv;
     suu += u * u; svv += vv * vv;
   }
@@ -430,7 +451,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS) slab_row_obs_kernel(SlabArgs<T
     for (int m = 0; m < E; ++m) {
       const int y = t + TPF * m;
       if (y % sy == 0 && y / sy < nobs) {
-        const T u = z[m].x.lo(), vv = z[m].y.lo();
+        const T u = z[m].x, vv = z[m].y;
         obs[(x / sx) * nobs + y / sy] += obs_w * sqrt(u * u + vv * vv);  // single writer per launch
       }
     }
@@ -462,6 +483,7 @@ struct TransposeArgs {
   // if out_tab[0] != nullptr, output block j (logical rows j*out_rpb ...) starts at out_tab[j] instead of
   // out + j*out_blk: the blocks may live on different GPUs (peer-mapped receive buffers)
   void* out_tab[KF_MAX_PEERS];
+  int in_lg, out_lg;  // log2 of in_rpb / out_rpb (both are powers of two; filled in by the launcher)
 };
 
 template <typename V> __global__ void __launch_bounds__(256) transpose_kernel(const V* __restrict__ in, V* __restrict__ out,
@@ -474,17 +496,18 @@ template <typename V> __global__ void __launch_bounds__(256) transpose_kernel(co
 #pragma unroll
   for (int i = 0; i < 32; i += 8) {
     const int r = r0 + ty + i, c = c0 + tx;
-    if (r < p.R && c < p.Cn) tile[ty + i][tx] = in[(size_t)(r / p.in_rpb) * p.in_blk + (size_t)(r % p.in_rpb) * p.in_ld + c];
+    if (r < p.R && c < p.Cn)
+      tile[ty + i][tx] = in[(size_t)(r >> p.in_lg) * p.in_blk + (size_t)(r & (p.in_rpb - 1)) * p.in_ld + c];
   }
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < 32; i += 8) {
     const int c = c0 + ty + i, r = r0 + tx;
     if (r < p.R && c < p.Cn) {
-      const int blk = c / p.out_rpb;
+      const int blk = c >> p.out_lg;
       V* dst = p.out_tab[0] ? reinterpret_cast<V*>(p.out_tab[blk]) + (size_t)blockIdx.z * p.out_z
                             : out + (size_t)blk * p.out_blk;
-      dst[(size_t)(c % p.out_rpb) * p.out_ld + r] = tile[tx][ty + i];
+      dst[(size_t)(c & (p.out_rpb - 1)) * p.out_ld + r] = tile[tx][ty + i];
     }
   }
 }
