@@ -268,7 +268,19 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_scalar_kernel(S
 
     if constexpr (MODE == kSlabStage) {
       const bool use_h = (a.beta != (T)0);
-      Cx<T> v[E], w[E];
+      constexpr unsigned kColBytes = (unsigned)(N * sizeof(Cx<T>));
+      if (t0 == 0 && g == 0) {
+        // the update below reads this column of h and omega_hat right after the transform, and the next
+        // iteration starts with its advection column: have L2 fetch them meanwhile
+#pragma unroll 1
+        for (int gg = 0; gg < GROUPS; ++gg) {
+          if (use_h) prefetch_l2_bulk(hrow + (size_t)gg * N, kColBytes);
+          prefetch_l2_bulk(wrow + (size_t)gg * N, kColBytes);
+          if (cb + (int)gridDim.x < ncb)
+            prefetch_l2_bulk(a.advk + ((size_t)(cb + gridDim.x) * GROUPS + gg) * N, kColBytes);
+        }
+      }
+      Cx<T> v[E];
       const Cx<T>* arow = a.advk + (size_t)ql * N;
 #pragma unroll
       for (int m = 0; m < E; ++m) v[m] = ld_stream(arow + t + TPF * m);
@@ -276,21 +288,48 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_scalar_kernel(S
       asm volatile("" : "+r"(t));
       Cx<T> g0 = mk<T>((T)0, (T)0);
       if (t == 0) g0 = ldc(a.G + q);
-      rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
-                             [&](int, int kx, Cx<T> h) { if (live) stc(hrow + kx, h); },
-                             [&](int, int kx, Cx<T> wv) { if (live) stc(wrow + kx, wv); },
-                             [&](int, int kx) { return ld_stream(hrow + kx); },
-                             [&](int, int kx) { return ld_stream(wrow + kx); });
+      // rk_update_column (kernels.cuh), with the loads of h and omega_hat issued four rows at a time: the stores
+      // of one row may alias the loads of the next as far as the compiler knows, so row-by-row every row costs a
+      // full memory round trip
+      constexpr int MH = N / 2, kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3, RB = 4;
+      const T tf = (T)t;
+#pragma unroll
+      for (int mb = 0; mb < E; mb += RB) {
+        Cx<T> hh[RB], ww[RB];
+#pragma unroll
+        for (int j = 0; j < RB; ++j) {
+          const int kx = t + TPF * (mb + j);
+          hh[j] = use_h ? ld_stream(hrow + kx) : mk<T>((T)0, (T)0);
+          ww[j] = ld_stream(wrow + kx);
+        }
+#pragma unroll
+        for (int j = 0; j < RB; ++j) {
+          const int m = mb + j, kx = t + TPF * m;
+          Cx<T> h = v[m];
+          if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) h = mk<T>((T)0, (T)0);
+          if (m == 0) h = h + g0;  // g0 is zero except on row kx = 0 (t == 0)
+          if (use_h) h = h + a.beta * hh[j];
+          if (live) stc(hrow + kx, h);
+          const T p = wave_p<T, P>(tf, m);
+          const T lk = a.munu * (p * p + qf * qf);
+          const Cx<T> wn = fast_rcp((T)1 + lk) * (ww[j] + a.gdt * h - lk * ww[j]);
+          if (live) stc(wrow + kx, wn);
+        }
+      }
     }
 
 #pragma unroll 1
     for (int fld = 0; fld < 4; ++fld) {  // u_hat, gx_hat, v_hat, gy_hat = c * (i omega_hat), kernels.cuh pair_coef
       asm volatile("" : "+r"(t));
       const T tf = (T)t;
+      // omega_hat is read back (L2-hot: this thread stored it above) through a pointer the compiler cannot see
+      // through: no forwarding of the stored registers, no hoisting above the stores, but all E loads in flight
+      const Cx<T>* wr = wrow;
+      asm volatile("" : "+l"(wr) : : "memory");
       Cx<T> f[E];
 #pragma unroll
       for (int m = 0; m < E; ++m) {
-        const Cx<T> wv = reload(wrow + t + TPF * m);  // L2-hot: this thread stored it above
+        const Cx<T> wv = ldc(wr + t + TPF * m);
         const T p = wave_p<T, P>(tf, m);
         const T sp = p * a.scale, sq = qf * a.scale, ik2 = inv_k2<T>(p, qf);
         const T c = fld == 0 ? sq * ik2 : fld == 1 ? sp : fld == 2 ? -(sp * ik2) : sq;
