@@ -1,0 +1,97 @@
+"""CUDA path vs what the REFERENCE'S OWN SOURCE computes (tests/golden/reference_shim_64_re100.npz, produced by
+tests/golden/make_reference_golden.py from the unmodified reference files over NumPy stand-ins for jax / gymnax / flax).
+No oracle in between: the kernels are compared with the reference's numbers directly, through the env boundary
+(which calls the C ABI).  fp64 tolerances are round-off accumulated over 990 solver steps per env call; fp32 uses the
+north-star tolerance (1e-3 relative L2 on vorticity)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+REF = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_shim_64_re100.npz"))
+FLOW = dict(Re=100, grid_size=(64, 64))
+
+
+def rel_l2(a, b):
+    return float(np.linalg.norm(a - b) / np.linalg.norm(b))
+
+
+@pytest.mark.parametrize("dtype,tol", [("float64", 1e-9), ("float32", 1e-3)])
+def test_env_reset_and_steps_vs_reference_source(dtype, tol):
+    from hydrogym_b200 import KolmogorovFlow
+    env = KolmogorovFlow(dict(dt=1e-2, dtype=dtype, device="cuda:0"), FLOW)
+    assert (env.n_inner, env.n_outer) == (99, 10)
+    params = env.default_params
+    obs, state = env.reset_env(None, params)
+    assert rel_l2(state.omega_hat.cpu().numpy(), REF["env_reset_omega"]) < tol
+    assert rel_l2(state.trajectory.cpu().numpy(), REF["env_reset_traj"]) < tol
+    assert np.abs(obs.cpu().numpy() - REF["env_reset_obs"]).max() < tol * 10
+    for i, a in enumerate(REF["env_actions"]):
+        obs, state, reward, done, info = env.step_env(None, state, torch.tensor(a), params)
+        assert np.abs(obs.cpu().numpy() - REF["env_obs"][i]).max() < tol * 10, i
+        assert abs(float(reward) - float(REF["env_reward"][i])) < 1e-6
+        assert abs(float(info["mean_tke"]) / float(REF["env_mean_tke"][i]) - 1) < tol
+        assert bool(done) == bool(REF["env_done"][i]) and float(info["discount"]) == float(REF["env_discount"][i])
+        assert int(state.time) == int(REF["env_time"][i])
+    assert rel_l2(state.omega_hat.cpu().numpy(), REF["env_final_omega"]) < tol
+    assert rel_l2(state.trajectory.cpu().numpy(), REF["env_final_traj"]) < tol
+
+
+def test_solver_steps_vs_reference_source():
+    """1 / 10 / 100 RK4-CN solver steps at dt = 1e-3 from the reference's initial state, zero control and the docs' action."""
+    from hydrogym_b200 import FlowConfig
+    from hydrogym_b200.solver import KolmogorovStepper
+    w0 = np.asarray(FlowConfig(**FLOW).initialize_state()).astype(np.complex128)
+    assert rel_l2(w0, REF["omega0"]) < 1e-14
+    st = KolmogorovStepper(grid_size=(64, 64), Re=100, dt=1e-3, num_envs=2, dtype=torch.float64, device="cuda:0")
+    w = torch.from_numpy(np.stack([REF["omega0"], REF["omega0"]])).cuda().contiguous()
+    acts = torch.tensor([[0.0, 0.0, 0.0, 0.0], [-0.25, -0.03, 0.02, 0.01]], dtype=torch.float64, device="cuda")
+    done = 0
+    for n in (1, 10, 100):
+        out = st.rk_steps(w, acts, n - done)
+        w = w if out is None else out
+        done = n
+        assert rel_l2(w[0].cpu().numpy(), REF[f"zero_action_rk{n}"]) < 1e-11, n
+    assert rel_l2(w[1].cpu().numpy(), REF["action_rk100"]) < 1e-11
+    st.close()
+
+
+def test_gymnax_autoreset_and_vecenv_vs_reference_source():
+    from hydrogym_b200 import KolmogorovFlow
+    env = KolmogorovFlow(dict(dt=1e-2, dtype="float64", device="cuda:0"), FLOW)
+    p1 = env.default_params.replace(max_episode_steps=1)
+    obs_r, state_r = env.reset(None, p1)
+    obs, state, reward, done, info = env.step(None, state_r, torch.tensor(REF["env_actions"][0]), p1)
+    assert np.abs(obs.cpu().numpy() - REF["auto_obs"]).max() < 1e-9
+    assert rel_l2(state.omega_hat.cpu().numpy(), REF["auto_omega"]) < 1e-9
+    assert int(state.time) == int(REF["auto_time"]) and bool(done) == bool(REF["auto_done"])
+    assert abs(float(reward) - float(REF["auto_reward"])) < 1e-12
+    assert abs(float(info["mean_tke"]) - float(REF["auto_mean_tke"])) < 1e-9
+    assert float(info["discount"]) == float(REF["auto_discount"])
+    # VecEnv: two environments, different actions (E:609-613)
+    p = env.default_params
+    vobs, vstate = env.reset(None, p, num_envs=2)
+    assert np.abs(vobs.cpu().numpy() - REF["vec_reset_obs"]).max() < 1e-9
+    vobs, vstate, vrew, vdone, vinfo = env.step(None, vstate, torch.from_numpy(REF["vec_actions"]), p)
+    assert rel_l2(vstate.omega_hat.cpu().numpy(), REF["vec_omega"]) < 1e-9
+    assert np.abs(vobs.cpu().numpy() - REF["vec_obs"]).max() < 1e-9
+    assert np.abs(vrew.cpu().numpy() - REF["vec_reward"]).max() < 1e-12
+    assert np.abs(vinfo["mean_tke"].cpu().numpy() - REF["vec_mean_tke"]).max() < 1e-9
+    assert vstate.time.tolist() == REF["vec_time"].tolist() and not bool(vdone.any())
+
+
+def test_diagnostics_vs_reference_utils():
+    from hydrogym_b200 import diagnostics as D
+    w = torch.from_numpy(np.asarray(REF["env_reset_omega"])).cuda()
+    uh, vh = D.compute_velocity_fft(w)
+    assert rel_l2(uh.cpu().numpy(), REF["diag_uhat"]) < 1e-13 and rel_l2(vh.cpu().numpy(), REF["diag_vhat"]) < 1e-13
+    assert abs(float(D.compute_energy_dissipation(w, 1.0 / 100)) / float(REF["diag_dissipation"]) - 1) < 1e-10
+    assert np.abs(D.compute_divergence(w).cpu().numpy() - REF["diag_divergence"]).max() < 1e-11
+    assert abs(float(D.compute_real_velocity_point(w, 8, 24)) - float(REF["diag_point_velocity"])) < 1e-11
+    modes = ((3, 4), (-2, 5), (0, 4))
+    em = np.array([float(D.compute_energy_mode(uh, vh, a, b, 64, 64)) for a, b in modes])
+    vm = np.array([float(D.compute_velocity_mode(uh, vh, a, b, 64, 64)) for a, b in modes])
+    assert np.allclose(em, REF["diag_energy_mode"], rtol=1e-11, atol=0) and np.allclose(vm, REF["diag_velocity_mode"], rtol=1e-11, atol=0)
