@@ -1,6 +1,15 @@
 """NumPy restatement of the reference's Kolmogorov-flow env step (test oracle).
 
-TEST INFRASTRUCTURE ONLY -- see ``oracle/__init__.py``.  PARITY UNPINNED.
+TEST INFRASTRUCTURE ONLY -- see ``oracle/__init__.py``.
+
+PINNED against the reference's own source: ``tests/golden/make_reference_golden.py``
+imports the UNMODIFIED reference files from ``/root/reference`` over NumPy stand-ins
+for the absent third-party modules (jax / flax / gymnax / chex / tree_math,
+``tests/golden/jax_numpy_shim.py``) and records their fp64 outputs in
+``tests/golden/reference_shim_64_re100.npz``; ``tests/test_reference_shim.py`` holds
+every function below to those vectors at round-off (<= 1e-12 per solver step,
+<= 1e-10 after 3 960 solver steps).  Not pinned: real jaxlib/XLA floating-point
+ordering (JAX itself is not installable here) -- fp64 round-off level only.
 
 Every function cites the reference lines it follows, with the tags of SURVEY.md:
   K = hydrogym/jax/envs/kolmogorov.py      S = hydrogym/jax/solvers/base.py

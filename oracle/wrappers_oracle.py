@@ -1,6 +1,7 @@
 """TEST INFRASTRUCTURE -- NumPy restatement of the reference's wrapper arithmetic (hydrogym/jax/env_core.py).
-Only tests/ may import this.  Parity unpinned (the reference ships no test for these wrappers; jax is not
-installable here): the functions below follow the cited lines statement by statement.
+Only tests/ may import this.  Pinned: tests/test_reference_shim.py drives the reference's own env_core.py wrapper
+stack (unmodified, over the NumPy stand-ins of tests/golden/jax_numpy_shim.py) and these functions with the same
+scripted environment and compares at 1e-11; the functions below follow the cited lines statement by statement.
 
 Each function maps (previous wrapper state, what the wrapped env returned this step) -> (outputs, new state)."""
 import numpy as np
