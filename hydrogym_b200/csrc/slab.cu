@@ -220,11 +220,12 @@ const SlabOps* find_slab_ops(int dtype, int N) {
 #endif
   static const SlabOps d256 = SlabImpl<double, Plan<256, 16, 16, 16>, 8, 8, Plan<128, 8, 16, 8>, 16>::make();
   static const SlabOps d1024 = SlabImpl<double, Plan<1024, 64, 16, 4, 16>, 2, 2, Plan<512, 32, 8, 8, 8>, 4>::make();
+  static const SlabOps d4096 = SlabImpl<double, Plan<4096, 256, 16, 16, 16>, 1, 1, Plan<2048, 128, 16, 8, 16>, 1>::make();
   const bool f = dtype == KF_F32;
   switch (N) {
     case 256: return f ? &f256 : &d256;
     case 1024: return f ? &f1024 : &d1024;
-    case 4096: return f ? &f4096 : nullptr;
+    case 4096: return f ? &f4096 : &d4096;
     case 8192: return f ? &f8192 : nullptr;
     default: return nullptr;
   }
@@ -279,7 +280,7 @@ int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks) {
   if (cfg->N != cfg->M) return fail("kf_slab_create: only square grids are supported (N == M)");
   if (cfg->dtype != KF_F32 && cfg->dtype != KF_F64) return fail("kf_slab_create: dtype must be KF_F32 or KF_F64");
   const SlabOps* ops = find_slab_ops(cfg->dtype, cfg->N);
-  if (!ops) return fail("kf_slab_create: grid size must be 256 or 1024 (fp32, fp64), 4096 or 8192 (fp32)");
+  if (!ops) return fail("kf_slab_create: grid size must be 256, 1024 or 4096 (fp32, fp64) or 8192 (fp32)");
   if (nranks < 1 || (nranks & (nranks - 1)) != 0) return fail("kf_slab_create: nranks must be a power of two");
   if (rank < 0 || rank >= nranks) return fail("kf_slab_create: rank out of range");
   if (cfg->N / 2 / nranks < 8) return fail("kf_slab_create: need at least 8 packed columns per rank");

@@ -3,8 +3,9 @@
     python tests/golden/make_golden.py
 
 The reference ships no golden data for the JAX Kolmogorov path and JAX cannot be
-installed here, so these vectors are ORACLE-generated ("parity unpinned").
-They freeze the oracle's behaviour: CPU tests check the oracle still reproduces them,
+installed here, so these vectors are ORACLE-generated.  The oracle itself is pinned against the
+reference's own source by make_reference_golden.py / reference_shim_64_re100.npz.
+They freeze the oracle's behaviour (including the fp32 cases): CPU tests check the oracle still reproduces them,
 GPU tests check the CUDA path against them.
 """
 import os
