@@ -65,11 +65,14 @@ template <typename X, int TC> struct ColExSplit {
 template <typename X, int TPF> struct RowEx {
   static constexpr bool kSplit = false;
   Cx<X>* sm;
+  int bar = 0;  // > 0: named barrier of this group's TPF threads (groups of one CTA run out of phase); 0: whole CTA
   __device__ __forceinline__ static int pad(int pos) { return pos + (pos >> 4); }
   __device__ __forceinline__ void store(int pos, Cx<X> a) { stc(sm + pad(pos), a); }
   __device__ __forceinline__ Cx<X> load(int pos) { return ldc(sm + pad(pos)); }
   __device__ __forceinline__ void sync() {
-    if (TPF <= 32) __syncwarp(); else __syncthreads();
+    if (TPF <= 32) __syncwarp();
+    else if (bar == 0) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(TPF) : "memory");
   }
 };
 

@@ -7,6 +7,7 @@
 
 #include <cmath>
 #include <string>
+#include <cstdlib>
 #include <vector>
 
 #include "slab.cuh"
@@ -60,19 +61,20 @@ struct SlabCtx {
   bool ipc_opened[KF_MAX_PEERS] = {};
   bool p2p = false;
   int sms = 148;
+  int row_prefetch = 1;  // KF_SLAB_ROW_PREFETCH=0 switches the row kernel's L2 prefetch off (A/B measurements)
   // the one-CTA kernel of the packed column runs beside the main column kernel on its own stream
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
-template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> struct SlabImpl {
+template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS, int CMINB = 2, int TWS = 0> struct SlabImpl {
   static_assert(PH::L * 2 == P::L, "the row kernel's plan is half the grid size");
   using C = kf::Cx<T>;
   using C2 = kf::Cx<typename kf::PairOf<T>::type>;
   static constexpr int N = P::L, MH = N / 2;
   static size_t smem(int groups) { return sizeof(C2) * groups * kf::slab_exchange_elems<N>() + sizeof(C) * (size_t)N; }
 
-  static size_t smem_scalar() { return kf::slab_scalar_smem_bytes<T, N, GROUPS>(); }
+  static size_t smem_scalar() { return kf::slab_scalar_smem_bytes<T, N, GROUPS, TWS>(); }
   static size_t smem_obs() { return sizeof(C) * (RGROUPS * kf::slab_exchange_elems<N>() + (size_t)N); }
 
   static cudaError_t prepare() {
@@ -80,8 +82,8 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
 #define KF_ATTR(k, bytes)                                                                              \
   e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes));              \
   if (e != cudaSuccess) return e;
-    KF_ATTR((kf::slab_col_scalar_kernel<T, P, GROUPS, kf::kSlabStage, 2>), smem_scalar())
-    KF_ATTR((kf::slab_col_scalar_kernel<T, P, GROUPS, kf::kSlabInit, 2>), smem_scalar())
+    KF_ATTR((kf::slab_col_scalar_kernel<T, P, GROUPS, kf::kSlabStage, CMINB, TWS>), smem_scalar())
+    KF_ATTR((kf::slab_col_scalar_kernel<T, P, GROUPS, kf::kSlabInit, CMINB, TWS>), smem_scalar())
     KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabStage, true, 1>), smem(1))
     KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabInit, true, 1>), smem(1))
     KF_ATTR((kf::slab_row_half_kernel<T, PH, HGROUPS, 2>), (kf::slab_half_smem_bytes<T, PH::L, HGROUPS>()))
@@ -103,6 +105,7 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
     a.dealias = c.cfg.dealias;
     a.q0 = c.rank * c.Q; a.x0 = c.rank * c.X;
     a.Q = c.Q; a.X = c.X; a.lgQ = c.lgQ;
+    a.row_prefetch = c.row_prefetch;
     return a;
   }
 
@@ -114,7 +117,7 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
   }
 
   template <int MODE> static void col_kernels(const SlabCtx& c, const kf::SlabArgs<T>& a, cudaStream_t s) {
-    auto main_k = kf::slab_col_scalar_kernel<T, P, GROUPS, MODE, 2>;
+    auto main_k = kf::slab_col_scalar_kernel<T, P, GROUPS, MODE, CMINB, TWS>;
     const int threads = P::TPF * GROUPS;
     if (c.rank == 0) {
       cudaEventRecord(c.ev_fork, s);
@@ -207,7 +210,8 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS> s
 
 const SlabOps* find_slab_ops(int dtype, int N) {
   using kf::Plan;
-  // <dtype, column plan (length N), column groups, obs-row groups, row plan (length N/2), row groups>
+  // <dtype, column plan (length N), column groups, obs-row groups, row plan (length N/2), row groups
+  //  [, column-kernel min CTAs per SM, twiddles of the column kernel in shared memory + per-group named barriers]>
   static const SlabOps f256 = SlabImpl<float, Plan<256, 16, 16, 16>, 8, 8, Plan<128, 8, 16, 8>, 16>::make();
   static const SlabOps f1024 = SlabImpl<float, Plan<1024, 64, 16, 4, 16>, 2, 2, Plan<512, 32, 8, 8, 8>, 4>::make();
   static const SlabOps f4096 = SlabImpl<float, Plan<4096, 256, 16, 16, 16>, 1, 1, Plan<2048, 128, 16, 8, 16>, 1>::make();
@@ -215,8 +219,15 @@ const SlabOps* find_slab_ops(int dtype, int N) {
   static const SlabOps f8192 =
       SlabImpl<float, Plan<8192, 512, 16, 16, 2, 16>, 1, 1, Plan<4096, 512, 8, 8, 8, 8>, 1>::make();
 #else
+#ifdef KF_SLAB_COL_2CTA
+  // column kernel as two 512-thread CTAs per SM, twiddles through L1 (measured 815 us per sub-stage vs 790 below)
   static const SlabOps f8192 =
       SlabImpl<float, Plan<8192, 512, 16, 16, 2, 16>, 1, 1, Plan<4096, 256, 16, 16, 16>, 1>::make();
+#else
+  // column kernel: one 1024-thread CTA per SM, two groups on named barriers, twiddles in shared memory
+  static const SlabOps f8192 =
+      SlabImpl<float, Plan<8192, 512, 16, 16, 2, 16>, 2, 1, Plan<4096, 256, 16, 16, 16>, 1, 1, 1>::make();
+#endif
 #endif
   static const SlabOps d256 = SlabImpl<double, Plan<256, 16, 16, 16>, 8, 8, Plan<128, 8, 16, 8>, 16>::make();
   static const SlabOps d1024 = SlabImpl<double, Plan<1024, 64, 16, 4, 16>, 2, 2, Plan<512, 32, 8, 8, 8>, 4>::make();
@@ -309,6 +320,7 @@ int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks) {
   while ((1 << c.lgQ) < c.Q) ++c.lgQ;
   const size_t el = ops->elem, qn = (size_t)c.Q * c.N;
   c.sms = prop.multiProcessorCount;
+  if (const char* e = getenv("KF_SLAB_ROW_PREFETCH")) c.row_prefetch = atoi(e) != 0;
   int rc = 0;
   {
     cudaError_t e = cudaStreamCreateWithFlags(&c.side, cudaStreamNonBlocking);

@@ -48,6 +48,7 @@ template <typename T> struct SlabArgs {
   int q0;               // global packed-column index of local column 0 (rank * Q)
   int x0;               // global x of local row 0 (rank * X)
   int Q, X, lgQ;
+  int row_prefetch;     // slab_row_half_kernel: L2 bulk prefetch of the next pair of field rows (KF_SLAB_ROW_PREFETCH)
 };
 
 // split exchange of one FFT group over a padded buffer of lane values (real parts, then imaginary parts)
@@ -233,8 +234,8 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
 // memory through L1 (the table is shared by both CTAs; the streaming operands bypass or leave L1 early).
 // grid: persistent over the Q local columns (global column 0 is computed but not stored).
 // ---------------------------------------------------------------------------
-template <typename T, int N, int GROUPS> __host__ __device__ constexpr size_t slab_scalar_smem_bytes() {
-  return sizeof(Cx<T>) * GROUPS * slab_exchange_elems<N>();
+template <typename T, int N, int GROUPS, int TWS = 0> __host__ __device__ constexpr size_t slab_scalar_smem_bytes() {
+  return sizeof(Cx<T>) * (GROUPS * slab_exchange_elems<N>() + (TWS ? (size_t)N : 0));
 }
 __device__ __forceinline__ Cx<float> ld_stream(const Cx<float>* p) {
   const float2 v = __ldcs(reinterpret_cast<const float2*>(p));
@@ -245,7 +246,12 @@ __device__ __forceinline__ Cx<double> ld_stream(const Cx<double>* p) {
   return mk<double>(v.x, v.y);
 }
 
-template <typename T, class P, int GROUPS, int MODE, int MINB>
+// TWS = 1: the twiddle table is copied to shared memory once per CTA and the groups of the CTA synchronise on their own
+// named barriers, so ONE CTA of GROUPS = 2 transforms per SM (1024 threads at 8192 points) replaces the two CTAs: the
+// same two out-of-phase transforms per SM, but the 15 twiddles a thread needs per pass come from shared memory instead
+// of an L1 that the streaming operands keep evicting (ncu: long_scoreboard on the first use of each twiddle was 37 % of
+// the stall samples of the two-CTA form).
+template <typename T, class P, int GROUPS, int MODE, int MINB, int TWS = 0>
 __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_scalar_kernel(SlabArgs<T> a) {
   constexpr int N = P::L, E = P::E, TPF = P::TPF;
   constexpr size_t EXN = slab_exchange_elems<N>();
@@ -253,6 +259,13 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_scalar_kernel(S
   const int g = threadIdx.x / TPF, t0 = threadIdx.x % TPF;
   RowEx<T, TPF> ex{reinterpret_cast<Cx<T>*>(smem_raw) + (size_t)g * EXN};
   const Cx<T>* __restrict__ tw = a.tw;
+  if constexpr (TWS != 0) {
+    Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw) + (size_t)GROUPS * EXN;
+    for (int i = threadIdx.x; i < N; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
+    __syncthreads();
+    tw = s_tw;
+    if (GROUPS > 1 && TPF > 32) ex.bar = 1 + g;
+  }
 
   const int ncb = a.Q / GROUPS;
 #pragma unroll 1
@@ -329,7 +342,11 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_scalar_kernel(S
       Cx<T> f[E];
 #pragma unroll
       for (int m = 0; m < E; ++m) {
+#ifdef KF_SLAB_WCG
+        const Cx<T> wv = reload(wr + t + TPF * m);  // L2 only: the 64 KB row must not evict the twiddle table from L1
+#else
         const Cx<T> wv = ldc(wr + t + TPF * m);
+#endif
         const T p = wave_p<T, P>(tf, m);
         const T sp = p * a.scale, sq = qf * a.scale, ik2 = inv_k2<T>(p, qf);
         const T c = fld == 0 ? sq * ik2 : fld == 1 ? sp : fld == 2 ? -(sp * ik2) : sq;
@@ -390,6 +407,16 @@ __global__ void __launch_bounds__(PH::TPF* GROUPS, MINB) slab_row_half_kernel(Sl
       // planes (u, gx) for pair 0, (v, gy) for pair 1, packed into the two lanes as they are loaded
       const Cx<T>* F0 = a.fx + (size_t)(2 * pair) * a.X * Q + roff;
       const Cx<T>* F1 = F0 + (size_t)a.X * Q;
+      if (a.row_prefetch && t < 2 * (H >> lgQ)) {
+        // the two plane rows this group transforms NEXT (pair 1 of this row, or pair 0 of the CTA's next row block):
+        // one bulk L2 prefetch per plane and per peer block, issued before this pair's own loads
+        const int nrb_next = rb + (int)gridDim.x;
+        if (pair == 0 || nrb_next < nrb) {
+          const size_t nroff = pair == 0 ? roff : (size_t)(nrb_next * GROUPS + g) * Q;
+          const Cx<T>* nx = a.fx + (size_t)(2 * (1 - pair) + (t & 1)) * a.X * Q + nroff + (size_t)(t >> 1) * blk;
+          prefetch_l2_bulk(nx, (unsigned)(Q * sizeof(Cx<T>)));
+        }
+      }
       auto ldp = [&](unsigned off) {
         const Cx<T> p0 = ldc(F0 + off), p1 = ldc(F1 + off);
         return mk<L2>(L2(p0.x, p1.x), L2(p0.y, p1.y));
