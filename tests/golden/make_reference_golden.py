@@ -16,6 +16,9 @@ third-party modules (`jax`, `flax`, `gymnax`, `chex`, `tree_math`, ...) replaced
 * the wrapper stack of `env_core.py` (LogWrapper, ClipAction, NormalizeVecObservation, NormalizeVecReward) over a
   scripted environment.
 
+* (second file, `reference_shim_sizes.npz`) the bench's own synthetic initial vorticity and action through 50 solver steps
+  at 128^2 Re = 100 (configs[1]) and 20 at 256^2 Re = 1000 (configs[2]).
+
 The file `reference_shim_64_re100.npz` written here is what `tests/test_reference_shim.py` holds the oracle to.
 The GPU box has no `/root/reference`: only the committed `.npz` travels.
 """
@@ -187,6 +190,32 @@ def main():
     path = os.path.join(HERE, "reference_shim_64_re100.npz")
     np.savez_compressed(path, **{k: np.asarray(v) for k, v in out.items()})
     print("wrote", path, os.path.getsize(path), "bytes,", len(out), "arrays")
+
+    # ---- the bench's own synthetic inputs (bench.synthetic_omega_hat / synthetic_actions, regenerated from their seeds
+    # by the tests) through the reference's solver at configs[1] (128^2, Re = 100) and configs[2] (256^2, Re = 1000)
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    import bench
+    sizes = {}
+    for N, Re, n_rk in ((128, 100, 50), (256, 1000, 20)):
+        env = KolmogorovFlow(None, dict(Re=Re, grid_size=(N, N)))
+        w = jnp.asarray(bench.synthetic_omega_hat(N, 0, np.float64))
+        act = bench.synthetic_actions(1, 1, np.float64)[0][0]
+        cf = env._control_field(jnp.clip(jnp.array(act), -0.5, 0.5), env.default_params)
+        step = env.integrator.RK4_CN(control_field=cf)
+        for _ in range(n_rk):
+            w = step(w)
+        w = np.asarray(w)
+        sizes[f"n{N}_steps"] = np.array(n_rk)
+        sizes[f"n{N}_action"] = act
+        sizes[f"n{N}_norm"] = np.array(np.linalg.norm(w))
+        sizes[f"n{N}_sum"] = np.array(w.sum())
+        if N == 128:
+            sizes["n128_omega"] = w
+        else:  # low-wavenumber block |kx| <= 32, ky <= 32 (the fixture stays small) + the two scalars above
+            sizes["n256_omega_low"] = w[np.r_[0:33, N - 32:N]][:, :33]
+    path = os.path.join(HERE, "reference_shim_sizes.npz")
+    np.savez_compressed(path, **sizes)
+    print("wrote", path, os.path.getsize(path), "bytes")
 
 
 def _takes(cls, name):

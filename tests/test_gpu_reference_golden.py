@@ -12,6 +12,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 REF = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_shim_64_re100.npz"))
+SIZES = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_shim_sizes.npz"))
 FLOW = dict(Re=100, grid_size=(64, 64))
 
 
@@ -99,3 +100,25 @@ def test_diagnostics_vs_reference_utils():
     em = np.array([float(D.compute_energy_mode(uh, vh, a, b, 64, 64)) for a, b in modes])
     vm = np.array([float(D.compute_velocity_mode(uh, vh, a, b, 64, 64)) for a, b in modes])
     assert np.allclose(em, REF["diag_energy_mode"], rtol=1e-11, atol=0) and np.allclose(vm, REF["diag_velocity_mode"], rtol=1e-11, atol=0)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-11), (torch.float32, 2e-4)])
+@pytest.mark.parametrize("N,Re", [(128, 100), (256, 1000)])
+def test_bench_inputs_vs_reference_solver(N, Re, dtype, tol):
+    """bench.py's synthetic vorticity / action at configs[1] (128^2, Re = 100, 50 solver steps) and configs[2]
+    (256^2, Re = 1000, 20 solver steps) against the reference's own solver run on the same arrays."""
+    import bench
+    from hydrogym_b200.solver import KolmogorovStepper
+    npdt = np.float64 if dtype == torch.float64 else np.float32
+    w = torch.from_numpy(np.stack([bench.synthetic_omega_hat(N, 0, npdt)] * 2)).cuda().contiguous()
+    act = bench.synthetic_actions(1, 1, np.float64)[0][0]
+    acts = torch.tensor(np.stack([act, act]), dtype=dtype, device="cuda")
+    st = KolmogorovStepper(grid_size=(N, N), Re=Re, dt=1e-3, num_envs=2, dtype=dtype, device="cuda:0")
+    st.rk_steps(w, acts, int(SIZES[f"n{N}_steps"]))
+    got = w[1].cpu().numpy().astype(np.complex128)
+    st.close()
+    assert abs(np.linalg.norm(got) / float(SIZES[f"n{N}_norm"]) - 1) < tol
+    if N == 128:
+        assert rel_l2(got, SIZES["n128_omega"]) < tol
+    else:
+        assert rel_l2(got[np.r_[0:33, N - 32:N]][:, :33], SIZES["n256_omega_low"]) < tol

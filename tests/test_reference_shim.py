@@ -20,6 +20,7 @@ from oracle import wrappers_oracle as wo
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF = np.load(os.path.join(HERE, "golden", "reference_shim_64_re100.npz"))
+SIZES = np.load(os.path.join(HERE, "golden", "reference_shim_sizes.npz"))
 FLOW = dict(Re=100, grid_size=(64, 64))
 ACTION = np.array([-0.25, -0.03, 0.02, 0.01])
 
@@ -126,6 +127,24 @@ def test_diagnostics_match_reference_utils():
     mine = np.array([orc.compute_energy_mode(uh, vh, a, b, 64, 64) for a, b in modes])
     assert np.allclose(mine, REF["diag_energy_mode"], rtol=1e-12, atol=0)
     assert abs(float(orc.compute_real_velocity_point(uh, vh, 8, 24)) - float(REF["diag_point_velocity"])) < 1e-13
+
+
+@pytest.mark.parametrize("N,Re", [(128, 100), (256, 1000)])
+def test_bench_inputs_through_reference_solver(N, Re):
+    """bench.py's synthetic vorticity / action (regenerated from their seeds) at configs[1] and configs[2]."""
+    import bench
+    env = orc.KolmogorovFlow(flow_config=dict(Re=Re, grid_size=(N, N)))
+    w = bench.synthetic_omega_hat(N, 0, np.float64)
+    act = bench.synthetic_actions(1, 1, np.float64)[0][0]
+    assert np.array_equal(act, SIZES[f"n{N}_action"])
+    ch = env.equation.control_term(w, env._control_field(env._clip_action(act, env.default_params), env.default_params))
+    w = env.integrator.rk_steps(w, int(SIZES[f"n{N}_steps"]), ch)
+    assert abs(np.linalg.norm(w) / float(SIZES[f"n{N}_norm"]) - 1) < 1e-12
+    assert abs(w.sum() - complex(SIZES[f"n{N}_sum"])) < 1e-9 * abs(complex(SIZES[f"n{N}_sum"]))
+    if N == 128:
+        assert rel(w, SIZES["n128_omega"]) < 1e-12
+    else:
+        assert rel(w[np.r_[0:33, N - 32:N]][:, :33], SIZES["n256_omega_low"]) < 1e-12
 
 
 # ------------------------------------------------------------------------------------------ wrapper stack
