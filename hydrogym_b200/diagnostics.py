@@ -91,3 +91,23 @@ def compute_divergence(omega_hat):
     u, v = _velocity(omega_hat)
     div = torch.gradient(u, dim=1)[0] + torch.gradient(v, dim=2)[0]
     return div[0] if omega_hat.dim() == 2 else div
+
+
+def compute_tke(omega_hat):
+    """utils.py:175-194: turbulent kinetic energy sum(0.5 (|u - mean u|^2 + |v - mean v|^2)) / n^2 of one state (N, Mh)
+    or a batch (B, N, Mh), through the fused reward / observation kernel (``kf_reward_obs`` on a one-snapshot
+    trajectory: c2r of u_hat, v_hat, fp64 warp-shuffle sums)."""
+    from .solver import KolmogorovStepper
+    w = omega_hat[None] if omega_hat.dim() == 2 else omega_hat
+    rd = torch.float32 if w.dtype == torch.complex64 else torch.float64
+    st = KolmogorovStepper(grid_size=(w.shape[1], w.shape[1]), num_envs=w.shape[0], dtype=rd, device=w.device,
+                           n_inner=1, n_outer=1)
+    _, tke, _ = st.reward_obs(w[:, None].contiguous())
+    st.close()
+    return tke[0] if omega_hat.dim() == 2 else tke
+
+
+def compute_reward(omega_hat, actions):
+    """utils.py:197-210 as written: TKE minus the plain sum of the four actions (not the env's reward, K:462-470)."""
+    a = torch.as_tensor(actions, device=omega_hat.device)
+    return compute_tke(omega_hat) - (a[..., 0] + a[..., 1] + a[..., 2] + a[..., 3])

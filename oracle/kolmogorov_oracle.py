@@ -152,6 +152,16 @@ def compute_energy_mode(uhat, vhat, kx, ky, n, m):
     return 0.5 * (np.abs(uhat[..., kx % n, ky % m]) ** 2 + np.abs(vhat[..., kx % n, ky % m]) ** 2) / float(n * m) ** 2
 
 
+def compute_velocity_mode(uhat, vhat, kx, ky, n, m):
+    """U:104-121 (kx, ky integer wavenumbers)."""
+    return np.sqrt((np.abs(uhat[..., kx % n, ky % m]) ** 2 + np.abs(vhat[..., kx % n, ky % m]) ** 2) / np.float64(n * m) ** 2)
+
+
+def compute_reward(omega_hat, kx, ky, nu, n, actions):
+    """U:197-210: TKE minus the plain sum of the four actions."""
+    return compute_tke(omega_hat, kx, ky, n) - (actions[0] + actions[1] + actions[2] + actions[3])
+
+
 def energy_spectrum(omega_hat, kx, ky, nbins=None):
     """Radial sum of the per-mode energies of U:89-101 over the FULL plane: bin = round(|k|) on integer
     wavenumbers, the conjugate half (not stored by rfft) counted through weights 2 on 0 < ky < m/2.

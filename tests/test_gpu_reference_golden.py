@@ -96,6 +96,11 @@ def test_diagnostics_vs_reference_utils():
     assert abs(float(D.compute_energy_dissipation(w, 1.0 / 100)) / float(REF["diag_dissipation"]) - 1) < 1e-10
     assert np.abs(D.compute_divergence(w).cpu().numpy() - REF["diag_divergence"]).max() < 1e-11
     assert abs(float(D.compute_real_velocity_point(w, 8, 24)) - float(REF["diag_point_velocity"])) < 1e-11
+    assert abs(float(D.compute_tke(w)) - float(REF["diag_tke"])) < 1e-12
+    act = torch.tensor([-0.25, -0.03, 0.02, 0.01], dtype=torch.float64, device="cuda")
+    assert abs(float(D.compute_reward(w, act)) - float(REF["diag_compute_reward"])) < 1e-12
+    both = torch.stack([w, 2 * w])
+    assert np.allclose(D.compute_tke(both).cpu().numpy(), [float(REF["diag_tke"]), 4 * float(REF["diag_tke"])], rtol=1e-12)
     modes = ((3, 4), (-2, 5), (0, 4))
     em = np.array([float(D.compute_energy_mode(uh, vh, a, b, 64, 64)) for a, b in modes])
     vm = np.array([float(D.compute_velocity_mode(uh, vh, a, b, 64, 64)) for a, b in modes])

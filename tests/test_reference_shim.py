@@ -127,6 +127,9 @@ def test_diagnostics_match_reference_utils():
     mine = np.array([orc.compute_energy_mode(uh, vh, a, b, 64, 64) for a, b in modes])
     assert np.allclose(mine, REF["diag_energy_mode"], rtol=1e-12, atol=0)
     assert abs(float(orc.compute_real_velocity_point(uh, vh, 8, 24)) - float(REF["diag_point_velocity"])) < 1e-13
+    vm = np.array([orc.compute_velocity_mode(uh, vh, a, b, 64, 64) for a, b in modes])
+    assert np.allclose(vm, REF["diag_velocity_mode"], rtol=1e-12, atol=0)
+    assert abs(float(orc.compute_reward(w, env.kx, env.ky, env.flow.nu, 64, ACTION)) - float(REF["diag_compute_reward"])) < 1e-13
 
 
 @pytest.mark.parametrize("N,Re", [(128, 100), (256, 1000)])
