@@ -95,12 +95,14 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
   const bool use_h = (a.beta != (T)0);
   const size_t plane = (size_t)N * MH;
 
+  pdl_launch_dependents();
   if (tid == 0) {
     for (int i = 0; i < 3 * STAGES; ++i) mbar_init(bars + i, 1);
     fence_mbar_init();
   }
   for (int i = tid; i < N; i += TPF * TC) s_tw[i] = ldc(a.tw + i);
   __syncthreads();
+  pdl_wait();  // everything below reads the row kernel's advection rows or overwrites the fields it still reads
 
   // Work list: the nb tiles with tx == 0 first (they also carry the ky = M/2 column and cost more), then
   // the others.  CTA i takes positions i, i + gridDim.x, ...: every CTA gets at most one expensive tile

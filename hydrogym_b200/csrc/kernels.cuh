@@ -341,6 +341,14 @@ __device__ __forceinline__ void load_pair_hermitian(Cx<X>* z, const Cx<X>* __res
   load_pair_hermitian_at<X, P>(z, A, B, t, [](int k) { return k; });
 }
 
+// Programmatic dependent launch (the host sets cudaLaunchAttributeProgrammaticStreamSerialization when KF_PDL=1): a
+// kernel lets its successor in the stream start early (launch_dependents, first instruction) and the successor runs
+// its own prologue -- twiddle table to shared memory, mbarrier setup -- while this grid drains; it must not touch
+// anything the predecessor reads or writes before pdl_wait(), which returns once the predecessor grid has completed
+// and its writes are visible.  Both are no-ops in a launch without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // L2 prefetch of `bytes` (multiple of 16) starting at p: no destination, no completion to wait for
 __device__ __forceinline__ void prefetch_l2_bulk(const void* p, unsigned bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
@@ -371,6 +379,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) row_kernel(StageArgs<T> 
   const int b = gridDim.y - 1 - blockIdx.y;
   const int x0 = 2 * (blockIdx.x * GROUPS + g);
   const size_t plane = (size_t)N * MH;
+  pdl_launch_dependents();
 
   if (KF_ROW_AHEAD > 0 && threadIdx.x == 0) {
     // the rows of the CTA that will run KF_ROW_AHEAD launches later (2*GROUPS contiguous rows of fa and of fb):
@@ -386,6 +395,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) row_kernel(StageArgs<T> 
   }
   for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
   __syncthreads();
+  pdl_wait();  // the fields below are the column kernel's output; the advection rows we write are its input
 
   Cx<T> v[E];
 #pragma unroll

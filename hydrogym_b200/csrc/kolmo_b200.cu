@@ -89,6 +89,8 @@ struct Ctx {
   CUtensorMap tm_adv, tm_h, tm_w;
   bool use_tma = false;
   int tma_ctas = 0;
+  // programmatic dependent launch of the stage kernels (KF_PDL=1; see pdl_wait in kernels.cuh)
+  bool pdl = false;
   // CUDA graph of `graph_steps` RK steps on a full chunk
   cudaGraphExec_t graph = nullptr;
   int graph_steps = 0;
@@ -147,9 +149,20 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     if (mode == kf::kColStage) kf::col_kernel<T, P, TC, kf::kColStage, CB><<<grid, P::TPF * TC, col_smem(), s>>>(a);
     else kf::col_kernel<T, P, TC, kf::kColInit, CB><<<grid, P::TPF * TC, col_smem(), s>>>(a);
   }
+  // launch of a stage kernel, with the programmatic-serialization attribute when the handle asks for it
+  template <class K, class... A>
+  static void launch_stage(const Ctx& c, K kernel, dim3 grid, int threads, size_t smem, cudaStream_t s, A... kargs) {
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = grid; lc.blockDim = dim3(threads); lc.dynamicSmemBytes = smem; lc.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = c.pdl ? 1 : 0;
+    cudaLaunchKernelEx(&lc, kernel, kargs...);
+  }
   static void row(const Ctx& c, int nb, cudaStream_t s) {
     kf::StageArgs<T> a = args(c);
-    kf::row_kernel<T, P, GROUPS, RB><<<dim3(N / 2 / GROUPS, nb), P::TPF * GROUPS, row_smem(), s>>>(a);
+    launch_stage(c, kf::row_kernel<T, P, GROUPS, RB>, dim3(N / 2 / GROUPS, nb), P::TPF * GROUPS, row_smem(), s, a);
   }
   static void obs(const Ctx& c, int nb, double* acc, size_t acc_stride, void* obs_dev, double obs_w, cudaStream_t s) {
     kf::ObsArgs<T> a;
@@ -186,8 +199,8 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     a.beta = (T)st.beta; a.gdt = (T)st.gdt; a.munu = (T)st.munu; a.store_h = st.store_h;
     const int ntiles = nb * (MH / TC);
     const int grid = ntiles < c.tma_ctas ? ntiles : c.tma_ctas;
-    kf::col_tma_kernel<T, P, TC, TB, ST, TS><<<grid, P::TPF * TC, kf::ColTmaSmem<T, P, TC, ST>::bytes(), s>>>(
-        a, c.tm_adv, c.tm_h, c.tm_w, ntiles);
+    launch_stage(c, kf::col_tma_kernel<T, P, TC, TB, ST, TS>, dim3(grid), P::TPF * TC, kf::ColTmaSmem<T, P, TC, ST>::bytes(),
+                 s, a, c.tm_adv, c.tm_h, c.tm_w, ntiles);
   }
   static Ops make() {
     Ops o;
@@ -561,6 +574,7 @@ int setup_lane(Ctx& c, const kf_config* cfg, const Ops* ops, int chunk) {
   } else {
     KF_CUDA(cudaMemcpy(c.tw, t64.data(), el * c.N, cudaMemcpyHostToDevice));
   }
+  if (const char* e = std::getenv("KF_PDL")) c.pdl = std::atoi(e) != 0;
   if (!std::getenv("KF_NO_TMA")) return ops->tma_setup(c);
   return 0;
 }
