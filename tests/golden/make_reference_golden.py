@@ -187,6 +187,32 @@ def main():
     out["wrap_obs"], out["wrap_reward"], out["wrap_done"] = np.array(wobs), np.array(wrew), np.array(wdone)
     out["wrap_returns"], out["wrap_lengths"], out["wrap_returned"] = np.array(wret), np.array(wlen), np.array(wretd)
 
+    # FlattenObservationWrapper / TransformObservation / TransformReward (E:460-495, 585-607) over the same scripted
+    # dynamics with a 2-D observation (3, 2), one un-batched environment, 5 steps (one episode end)
+    class Scripted2D(Scripted):
+        def reset_env(self, key, params):
+            x, st = super().reset_env(key, params)
+            return jnp.outer(x, jnp.array([1.0, -2.0])), st
+
+        def step_env(self, key, state, action, params):
+            x, st, r, d, info = super().step_env(key, state, action, params)
+            return jnp.outer(x, jnp.array([1.0, -2.0])), st, r, d, info
+
+        def observation_space(self, params):
+            from gymnax.environments import spaces
+            return spaces.Box(-jnp.inf, jnp.inf, (3, 2))
+
+    fenv = env_core.FlattenObservationWrapper(Scripted2D())
+    assert fenv.observation_space(base.default_params).shape == (6,)
+    fenv = env_core.TransformReward(env_core.TransformObservation(fenv, lambda o: 2.0 * o + 1.0), lambda r: r - 1.0)
+    key1 = jnp.array([0, 5], dtype=np.uint32)
+    obs, st = fenv.reset(key1, base.default_params)
+    fobs, frew, fdone = [np.array(obs)], [], []
+    for t in range(5):
+        obs, st, rew, done, info = fenv.step(key1, st, jnp.array(acts[t][0]), base.default_params)
+        fobs.append(np.array(obs)), frew.append(np.array(rew)), fdone.append(np.array(done))
+    out["flat_key"], out["flat_obs"], out["flat_reward"], out["flat_done"] = np.array(key1), np.array(fobs), np.array(frew), np.array(fdone)
+
     path = os.path.join(HERE, "reference_shim_64_re100.npz")
     np.savez_compressed(path, **{k: np.asarray(v) for k, v in out.items()})
     print("wrote", path, os.path.getsize(path), "bytes,", len(out), "arrays")

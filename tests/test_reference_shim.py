@@ -210,6 +210,36 @@ def test_wrapper_stack_matches_reference_env_core():
     assert REF["wrap_done"].sum() >= 2 * B  # episodes really ended (auto-reset exercised)
 
 
+def test_flatten_and_transform_wrappers_match_reference_env_core():
+    """FlattenObservationWrapper -> TransformObservation -> TransformReward (E:460-495, 585-607) over a (3, 2) observation."""
+    class _Scripted2D(_ScriptedBatch):
+        W = np.array([1.0, -2.0])
+
+        def reset(self, key=None, params=None, num_envs=None):
+            obs, st = super().reset(key, params, num_envs)
+            return obs[:, :, None] * torch.from_numpy(self.W), st
+
+        def step(self, key, state, action, params=None):
+            obs, st, r, d, info = super().step(key, state, action, params)
+            return obs[:, :, None] * torch.from_numpy(self.W), st, r, d, info
+
+        def observation_space(self, params=None):
+            from hydrogym_b200.spaces import Box
+            return Box(-np.inf, np.inf, (3, 2))
+
+    env = _Scripted2D(REF["flat_key"][None])
+    flat = W.FlattenObservationWrapper(env)
+    assert flat.observation_space(None).shape == (6,)
+    w = W.TransformReward(W.TransformObservation(flat, lambda o: 2.0 * o + 1.0), lambda r: r - 1.0)
+    obs, st = w.reset(None, None)
+    assert obs.shape == (1, 6) and np.allclose(obs[0].numpy(), REF["flat_obs"][0], rtol=1e-13, atol=1e-13)
+    for t in range(5):
+        obs, st, r, d, info = w.step(None, st, torch.from_numpy(REF["wrap_actions"][t][:1]), None)
+        assert np.allclose(obs[0].numpy(), REF["flat_obs"][t + 1], rtol=1e-13, atol=1e-13), t
+        assert abs(float(r[0]) - float(REF["flat_reward"][t])) < 1e-12 and bool(d[0]) == bool(REF["flat_done"][t])
+    assert REF["flat_done"].sum() == 1
+
+
 @pytest.mark.skipif(not os.path.isdir("/root/reference/hydrogym/jax"), reason="reference tree only exists in the build container")
 def test_live_reference_source_agrees_with_fixture_and_oracle():
     """Re-runs a slice of the generator against /root/reference (fresh interpreter: the stand-ins touch sys.modules)."""
