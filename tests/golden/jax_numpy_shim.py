@@ -97,10 +97,6 @@ class _NumpyProxy(types.ModuleType):
 
 
 # ----------------------------------------------------------------------------------------------- pytrees
-def _is_leaf(x):
-    return not (isinstance(x, (tuple, list, dict)) or dataclasses.is_dataclass(x)) or x is None
-
-
 def tree_map(f, tree, *rest):
     if tree is None:
         return None
