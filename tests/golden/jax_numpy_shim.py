@@ -69,9 +69,23 @@ class JArray(np.ndarray):
         return self
 
 
+# x64 = False mimics JAX's DEFAULT mode (jax_enable_x64 off): every float64 / complex128 result is narrowed to
+# float32 / complex64 as it is produced, so the reference's arithmetic runs in single precision end to end
+# (NumPy >= 2 keeps float32 through np.fft and treats Python scalars as weak).  Set through install(x64=...).
+_X64 = True
+
+
 def _wrap(x):
-    if isinstance(x, np.ndarray) and not isinstance(x, JArray):
-        return x.view(JArray)
+    if isinstance(x, np.ndarray):
+        if not _X64 and x.dtype == np.float64:
+            x = x.astype(np.float32)
+        elif not _X64 and x.dtype == np.complex128:
+            x = x.astype(np.complex64)
+        return x if isinstance(x, JArray) else x.view(JArray)
+    if not _X64 and isinstance(x, np.float64):
+        return np.float32(x)
+    if not _X64 and isinstance(x, np.complex128):
+        return np.complex64(x)
     if isinstance(x, tuple):
         return tuple(_wrap(v) for v in x)
     if isinstance(x, list):
@@ -294,8 +308,11 @@ def _make_misc():
     return mods
 
 
-def install(reference_root="/root/reference"):
-    """Register the stand-ins (only for modules that are really absent) and put the reference on sys.path."""
+def install(reference_root="/root/reference", x64=True):
+    """Register the stand-ins (only for modules that are really absent) and put the reference on sys.path.
+    ``x64=False``: single precision throughout, as JAX runs without ``jax_enable_x64``."""
+    global _X64
+    _X64 = bool(x64)
     mods = {}
     mods.update(_make_jax())
     mods.update(_make_flax())

@@ -19,6 +19,8 @@ third-party modules (`jax`, `flax`, `gymnax`, `chex`, `tree_math`, ...) replaced
 * (second file, `reference_shim_sizes.npz`) the bench's own synthetic initial vorticity and action through 50 solver steps
   at 128^2 Re = 100 (configs[1]) and 20 at 256^2 Re = 1000 (configs[2]).
 
+* (third file, `reference_shim_64_re100_fp32.npz`) 1 / 10 / 100 solver steps in SINGLE precision (JAX's default mode).
+
 The file `reference_shim_64_re100.npz` written here is what `tests/test_reference_shim.py` holds the oracle to.
 The GPU box has no `/root/reference`: only the committed `.npz` travels.
 """
@@ -244,10 +246,41 @@ def main():
     print("wrote", path, os.path.getsize(path), "bytes")
 
 
+def main_fp32():
+    """The same reference source in SINGLE precision (JAX's default mode, `jax_enable_x64` off): a separate interpreter
+    (`python make_reference_golden.py --fp32`, spawned by main) because the precision switch is global to the stand-ins."""
+    jax_numpy_shim.install(x64=False)
+    import jax.numpy as jnp
+
+    from hydrogym.jax.envs.kolmogorov import KolmogorovFlow
+    env = KolmogorovFlow(None, FLOW)
+    w0 = env.flow.initialize_state()
+    assert w0.dtype == np.complex64 and env.kx.dtype == np.float32
+    out = {"omega0": w0}
+    cf = env._control_field(jnp.array(ACTION), env.default_params)
+    for name, control in (("zero_action", None), ("action", cf)):
+        step = env.integrator.RK4_CN(control_field=control)
+        w, done = w0, 0
+        for n in (1, 10, 100):
+            for _ in range(n - done):
+                w = step(w)
+            done = n
+            out[f"{name}_rk{n}"] = w
+        assert w.dtype == np.complex64
+    path = os.path.join(HERE, "reference_shim_64_re100_fp32.npz")
+    np.savez_compressed(path, **{k: np.asarray(v) for k, v in out.items()})
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
 def _takes(cls, name):
     import inspect
     return name in inspect.signature(cls.__init__).parameters
 
 
 if __name__ == "__main__":
-    main()
+    if "--fp32" in sys.argv:
+        main_fp32()
+    else:
+        main()
+        import subprocess
+        subprocess.check_call([sys.executable, os.path.abspath(__file__), "--fp32"])

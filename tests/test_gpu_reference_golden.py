@@ -64,6 +64,23 @@ def test_solver_steps_vs_reference_source():
     st.close()
 
 
+def test_single_precision_solver_steps_vs_reference_source():
+    """fp32 kernels vs the reference source run in JAX's default single precision (reference_shim_64_re100_fp32.npz):
+    north-star tolerance 1e-3 relative L2 after 100 solver steps."""
+    from hydrogym_b200.solver import KolmogorovStepper
+    ref32 = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_shim_64_re100_fp32.npz"))
+    st = KolmogorovStepper(grid_size=(64, 64), Re=100, dt=1e-3, num_envs=2, dtype=torch.float32, device="cuda:0")
+    w = torch.from_numpy(np.stack([ref32["omega0"], ref32["omega0"]])).cuda().contiguous()
+    acts = torch.tensor([[0.0, 0.0, 0.0, 0.0], [-0.25, -0.03, 0.02, 0.01]], dtype=torch.float32, device="cuda")
+    done = 0
+    for n in (1, 10, 100):
+        st.rk_steps(w, acts, n - done)
+        done = n
+        assert rel_l2(w[0].cpu().numpy(), ref32[f"zero_action_rk{n}"]) < 1e-3, n
+        assert rel_l2(w[1].cpu().numpy(), ref32[f"action_rk{n}"]) < 1e-3, n
+    st.close()
+
+
 def test_gymnax_autoreset_and_vecenv_vs_reference_source():
     from hydrogym_b200 import KolmogorovFlow
     env = KolmogorovFlow(dict(dt=1e-2, dtype="float64", device="cuda:0"), FLOW)

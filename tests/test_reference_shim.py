@@ -56,6 +56,23 @@ def test_rk4_cn_solver_steps():
     assert rel(env.integrator.rk_steps(REF["omega0"], 100, ch), REF["action_rk100"]) < 1e-12
 
 
+def test_single_precision_solver_steps():
+    """The reference source in JAX's DEFAULT precision (x64 off -> fp32 / complex64 end to end) vs the fp32 oracle."""
+    ref32 = np.load(os.path.join(HERE, "golden", "reference_shim_64_re100_fp32.npz"))
+    env = orc.KolmogorovFlow(flow_config=FLOW, dtype=np.float32)
+    w0 = env.flow.initialize_state()
+    assert w0.dtype == np.complex64 and ref32["omega0"].dtype == np.complex64 and rel(w0, ref32["omega0"]) < 1e-6
+    ch = env.equation.control_term(w0, env._control_field(ACTION.astype(np.float32), env.default_params))
+    for name, control in (("zero_action", None), ("action", ch)):
+        w, done = ref32["omega0"], 0
+        for n in (1, 10, 100):
+            w = env.integrator.rk_steps(w, n - done, control)
+            done = n
+            assert w.dtype == np.complex64 and rel(w, ref32[f"{name}_rk{n}"]) < 2e-6, (name, n)
+    # and single vs double precision of the reference itself stays inside the north-star fp32 tolerance
+    assert rel(ref32["action_rk100"], REF["action_rk100"]) < 1e-4
+
+
 def test_solve_step_counts_and_snapshots():
     env = orc.KolmogorovFlow(flow_config=FLOW)
     cf = env._control_field(ACTION, env.default_params)
