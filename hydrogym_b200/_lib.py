@@ -23,6 +23,7 @@ SYMBOLS = (
     "kf_slab_export", "kf_slab_exchange_bytes", "kf_slab_col", "kf_slab_row", "kf_slab_obs",
     "kf_slab_launch_count", "kf_slab_workspace_bytes", "kf_energy_spectrum",
     "kf_slab_p2p_init", "kf_slab_p2p_attach", "kf_slab_p2p_attach_local", "kf_physical_fields",
+    "kf_set_control_field", "kf_nonlinear_terms", "kf_linear_terms", "kf_implicit_timestep", "kf_strain_diagnostics",
 )
 
 
@@ -98,6 +99,15 @@ def load():
         getattr(lib, name).restype = ctypes.c_int
     lib.kf_physical_fields.argtypes = [vp, vp, vp, ctypes.c_int, vp]
     lib.kf_physical_fields.restype = ctypes.c_int
+    lib.kf_set_control_field.argtypes = [vp, vp]
+    lib.kf_nonlinear_terms.argtypes = [vp, vp, vp, vp, vp]
+    cd, ci = ctypes.c_double, ctypes.c_int
+    lib.kf_linear_terms.argtypes = [ci, ci, ci, cd, vp, vp, vp]
+    lib.kf_implicit_timestep.argtypes = [ci, ci, ci, cd, cd, vp, vp, vp]
+    lib.kf_strain_diagnostics.argtypes = [ci, ci, ci, cd, vp, vp, vp, vp, vp]
+    for name in ("kf_set_control_field", "kf_nonlinear_terms", "kf_linear_terms", "kf_implicit_timestep",
+                 "kf_strain_diagnostics"):
+        getattr(lib, name).restype = ctypes.c_int
     lib.kf_energy_spectrum.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_int, vp]
     lib.kf_energy_spectrum.restype = ctypes.c_int
     _lib = lib

@@ -19,6 +19,16 @@ from __future__ import annotations
 import numpy as np
 
 
+def check_domain(domain_x, domain_y):
+    """The kernels work on integer wavenumbers (2*pi*kx = p), i.e. on the reference's default 2*pi-periodic box
+    (kolmogorov.py:33-34 DEFAULT_DOMAIN_X / _Y).  Any other domain would make the host-side forcing / control rows
+    and the device-side derivative and viscous operators disagree, so it is refused instead of silently mixed."""
+    for name, d in (("domain_x", domain_x), ("domain_y", domain_y)):
+        lo, hi = float(d[0]), float(d[1])
+        if lo != 0.0 or abs(hi - 2 * np.pi) > 1e-12:
+            raise ValueError(f"hydrogym_b200 supports the reference's default domain (0, 2*pi) only; got {name}={tuple(d)}")
+
+
 def step_counts(dt: float, end_time: float, save_n: int = 1):
     """(n_inner, n_outer) with the reference's Python float floor-division (base.py:100-103)."""
     if end_time < 1:

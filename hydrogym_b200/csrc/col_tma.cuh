@@ -2,23 +2,23 @@
 //
 // Same arithmetic as col_kernel<..., kColStage> (kernels.cuh), but the three input tiles of a
 // (environment, TC-column) tile -- advection rows, RK register h, omega_hat -- arrive in shared
-// memory through cp.async.bulk.tensor (TMA, SASS UTMALDG) a whole tile AHEAD of their use
-// (STAGES = 2 ring of {adv, h, w} buffers), and the updated h / omega_hat tiles leave through TMA
-// stores (UTMASTG) instead of 8-byte per-thread stores:
+// memory through cp.async.bulk.tensor (TMA, SASS UTMALDG) on one mbarrier each, one tile AHEAD of
+// their use: a CTA owns ONE {adv, h, w} buffer set and re-arms each buffer as soon as the current
+// tile has consumed it,
 //
-//   buffer    filled by TMA with     consumed by                   then reused as
-//   adv[s]    adv rows of tile i     first FFT pass (registers)    exchange buffer of the forward FFT, then the
-//                                                                  NEW h tile (TMA-stored to global)
-//   h[s]      h of tile i            RK accumulate                 split exchange buffer of the two lane-paired
-//                                                                  inverse FFTs (real, then imaginary parts)
-//   w[s]      omega_hat of tile i    Crank-Nicolson update         the NEW omega_hat tile: TMA-stored to global and
-//                                                                  read back by the prologue of the next stage
+//   buffer  filled by TMA with     consumed by                  then reused as
+//   adv     adv rows of tile i     first FFT pass (registers)   exchange buffer of the forward FFT; re-armed for
+//                                                               tile i + gridDim.x right after that FFT
+//   h       h of tile i            RK accumulate                split exchange buffer of the two lane-paired
+//                                                               inverse FFTs; re-armed at the end of the tile
+//   w       omega_hat of tile i    Crank-Nicolson update        the NEW omega_hat (read back by the prologue of
+//                                                               the next stage); re-armed at the end of the tile
 //
-// At the end of tile i thread 0 waits for the two TMA stores to have read their buffers and issues
-// the loads of tile i + 2*gridDim.x into the same stage; tile i + gridDim.x is already resident in
-// the other stage.  With STAGES = 1 (grids too large for two stages) adv is re-issued right after the
-// forward FFT and h / omega_hat after the last inverse FFT.  The lane-paired fields leave with
-// 128-bit coalesced stores.  One CTA = TPF*TC threads; grid = #SMs x resident CTAs.
+// so the advection load of the next tile overlaps the RK update and both inverse transforms of
+// this one.  Results leave with per-thread stores (64-bit h / omega_hat, 128-bit lane-paired fields, runs
+// of TC columns per row).  A two-stage ring with TMA stores (UTMASTG) was built and measured in round 1
+// (131.7 -> 139.5 us per launch at 256 envs: slower) and has been removed.
+// One CTA = TPF*TC threads; grid = #SMs x resident CTAs.
 #pragma once
 #include <cuda.h>  // CUtensorMap (type only; the encoder is fetched at run time)
 
@@ -58,46 +58,35 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       : "memory");
 }
 
-// 2-D tiled TMA store: dense [rows][inner] in smem -> box at (c0, c1); completion through the bulk async-group
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, int c0, int c1, const void* src) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(
-                   reinterpret_cast<uint64_t>(map)),
-               "r"(c0), "r"(c1), "r"(smem_u32(src))
-               : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-
-template <typename T, class P, int TC, int STAGES> struct ColTmaSmem {
+template <typename T, class P, int TC> struct ColTmaSmem {
   static constexpr int N = P::L;
   static constexpr size_t kTile = (size_t)N * TC * sizeof(Cx<T>);
   static_assert(kTile == col_exchange_bytes<T, N, TC>(), "a tile buffer doubles as the exchange buffer");
-  static constexpr size_t bytes() { return 3 * STAGES * kTile + 2 * (size_t)N * sizeof(Cx<T>) + 64; }
+  static constexpr size_t bytes() { return 3 * kTile + 2 * (size_t)N * sizeof(Cx<T>) + 64; }
 };
 
-template <typename T, class P, int TC, int MINB, int STAGES, bool TSTORE = (STAGES == 2)>
+template <typename T, class P, int TC, int MINB>
 __global__ void __launch_bounds__(P::TPF* TC, MINB)
     col_tma_kernel(StageArgs<T> a, const __grid_constant__ CUtensorMap m_adv, const __grid_constant__ CUtensorMap m_h,
                    const __grid_constant__ CUtensorMap m_w, int ntiles) {
-  static_assert(STAGES == 1 || STAGES == 2, "one or two input stages");
-  static_assert(!TSTORE || STAGES == 2, "TMA stores reuse the advection buffer of a two-stage ring");
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2, TILES = MH / TC;
   constexpr int RB = N < 256 ? N : 256, NBOX = N / RB;  // TMA box rows (<= 256)
   constexpr uint32_t kBytes = (uint32_t)((size_t)N * TC * sizeof(Cx<T>));
   constexpr size_t kTileEl = (size_t)N * TC;
   extern __shared__ __align__(1024) unsigned char smem_tma[];
-  Cx<T>* bufs = reinterpret_cast<Cx<T>*>(smem_tma);  // [STAGES][3][N*TC]: adv, h, w
-  Cx<T>* s_tw = bufs + 3 * STAGES * kTileEl;
+  Cx<T>* buf_adv = reinterpret_cast<Cx<T>*>(smem_tma);
+  Cx<T>* buf_h = buf_adv + kTileEl;
+  Cx<T>* buf_w = buf_h + kTileEl;
+  Cx<T>* s_tw = buf_w + kTileEl;
   Cx<T>* s_nyq = s_tw + N;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_nyq + N);  // [STAGES][3]: adv, h, w
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_nyq + N);  // [3]: adv, h, w
   const int tid = threadIdx.x, c = tid % TC, t = tid / TC;
   const bool use_h = (a.beta != (T)0);
   const size_t plane = (size_t)N * MH;
 
   pdl_launch_dependents();
   if (tid == 0) {
-    for (int i = 0; i < 3 * STAGES; ++i) mbar_init(bars + i, 1);
+    for (int i = 0; i < 3; ++i) mbar_init(bar + i, 1);
     fence_mbar_init();
   }
   for (int i = tid; i < N; i += TPF * TC) s_tw[i] = ldc(a.tw + i);
@@ -112,49 +101,35 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     if (pos < nb) { b = pos; tx = 0; }
     else { constexpr int TM1 = TILES > 1 ? TILES - 1 : 1; const int r = pos - nb; b = r / TM1; tx = 1 + (r - b * TM1); }
   };
-  auto issue = [&](Cx<T>* buf, const CUtensorMap* map, uint64_t* bar, int tile) {
+  auto issue = [&](Cx<T>* buf, const CUtensorMap* map, uint64_t* br, int tile) {
     int b, tx;
     decode(tile, b, tx);
-    mbar_expect_tx(bar, kBytes);
+    mbar_expect_tx(br, kBytes);
 #pragma unroll
     for (int r = 0; r < NBOX; ++r)
-      tma_load_2d(buf + (size_t)r * RB * TC, map, tx * TC * 2, b * N + r * RB, bar);
+      tma_load_2d(buf + (size_t)r * RB * TC, map, tx * TC * 2, b * N + r * RB, br);
   };
-  auto store_tile = [&](const CUtensorMap* map, const Cx<T>* buf, int b, int tx) {
-#pragma unroll
-    for (int r = 0; r < NBOX; ++r) tma_store_2d(map, tx * TC * 2, b * N + r * RB, buf + (size_t)r * RB * TC);
-  };
+  constexpr int km = ((MH + 1) * 2) / 3;  // 2/3 mask: columns ky >= km of the advection term are discarded
 
-  if (tid == 0) {
-    for (int s = 0; s < STAGES; ++s) {
-      const int tile = blockIdx.x + s * gridDim.x;
-      if (tile >= ntiles) break;
-      int b0, tx0;
-      decode(tile, b0, tx0);
-      if (!(a.dealias && tx0 * TC >= ((MH + 1) * 2) / 3))
-        issue(bufs + (3 * s + 0) * kTileEl, &m_adv, bars + 3 * s + 0, tile);
-      if (use_h) issue(bufs + (3 * s + 1) * kTileEl, &m_h, bars + 3 * s + 1, tile);
-      issue(bufs + (3 * s + 2) * kTileEl, &m_w, bars + 3 * s + 2, tile);
-    }
+  if (tid == 0 && (int)blockIdx.x < ntiles) {
+    int b0, tx0;
+    decode(blockIdx.x, b0, tx0);
+    if (!(a.dealias && tx0 * TC >= km)) issue(buf_adv, &m_adv, bar + 0, blockIdx.x);
+    if (use_h) issue(buf_h, &m_h, bar + 1, blockIdx.x);
+    issue(buf_w, &m_w, bar + 2, blockIdx.x);
   }
 
-  uint32_t it = 0, adv_phase = 0;  // adv_phase bit s: parity of the advection barrier of stage s
+  uint32_t it = 0, adv_phase = 0;  // adv_phase: parity of the advection barrier (masked tiles skip a phase)
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-    const int s = (STAGES == 2) ? (int)(it & 1u) : 0;
-    const uint32_t par = (STAGES == 2) ? ((it >> 1) & 1u) : (it & 1u);
-    Cx<T>* buf_adv = bufs + (3 * s + 0) * kTileEl;
-    Cx<T>* buf_h = bufs + (3 * s + 1) * kTileEl;
-    Cx<T>* buf_w = bufs + (3 * s + 2) * kTileEl;
-    uint64_t* bar = bars + 3 * s;
+    const uint32_t par = it & 1u;
     int b, tx;
     decode(tile, b, tx);
     const int q = tx * TC + c;
     const bool special = (tx == 0);  // CTA-uniform
-    const int next = tile + STAGES * gridDim.x;  // the tile that will reuse this stage
+    const int next = tile + gridDim.x;  // the tile that will reuse the buffers
     const bool has_next = next < ntiles;
-    // 2/3 mask on: the advection term of the columns ky >= km is discarded, so tiles made only of such columns
-    // neither load nor transform it (the row kernel does not write them)
-    constexpr int km = ((MH + 1) * 2) / 3;
+    // 2/3 mask on: tiles made only of columns ky >= km neither load nor transform the advection term (the row
+    // kernel does not write those columns)
     const bool masked_tile = a.dealias && tx * TC >= km;  // CTA-uniform
     bool next_masked = false;
     if (has_next && a.dealias) {
@@ -170,8 +145,8 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
 
     Cx<T> v[E];
     if (!masked_tile) {
-      mbar_wait(bar + 0, (adv_phase >> s) & 1u);
-      adv_phase ^= 1u << s;  // one phase per advection tile actually loaded into this stage
+      mbar_wait(bar + 0, adv_phase);
+      adv_phase ^= 1u;  // one phase per advection tile actually loaded
 #pragma unroll
       for (int m = 0; m < E; ++m) v[m] = ldc(buf_adv + (size_t)(t + TPF * m) * TC + c);
       __syncthreads();  // all rows are in registers before buf_adv becomes the exchange buffer
@@ -197,7 +172,7 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
       }
       __syncthreads();
     }
-    if (STAGES == 1 && tid == 0 && has_next && !next_masked) {  // single stage: buf_adv is needed first, refill it now
+    if (tid == 0 && has_next && !next_masked) {  // buf_adv is free: refill it for the next tile now
       fence_proxy_async();
       issue(buf_adv, &m_adv, bar + 0, next);
     }
@@ -206,33 +181,20 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     mbar_wait(bar + 2, par);
     {
       Cx<T> w[E];
-      if constexpr (TSTORE) {
-        // new h -> buf_adv, new omega_hat -> buf_w (in place); both tiles leave through TMA stores
-        rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
-                               [&](int, int kx, Cx<T> h) { stc(buf_adv + kx * TC + c, h); },
-                               [&](int, int kx, Cx<T> wn) { stc(buf_w + kx * TC + c, wn); },
-                               [&](int, int kx) { return ldc(buf_h + kx * TC + c); },
-                               [&](int, int kx) { return ldc(buf_w + kx * TC + c); });
-        fence_proxy_async();  // make the generic-proxy writes visible to the TMA engine
-        __syncthreads();      // ... and buf_h has been consumed: it becomes the exchange buffer
-        if (tid == 0) {
-          if (a.store_h) store_tile(&m_h, buf_adv, b, tx);
-          store_tile(&m_w, buf_w, b, tx);
-          bulk_commit();
-        }
-      } else {
-        Cx<T>* wmain = a.wmain + b * plane + q;
-        Cx<T>* hmain = a.hmain + b * plane + q;
-        rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
-                               [&](int, int kx, Cx<T> h) { if (a.store_h) stc(hmain + (size_t)kx * MH, h); },
-                               [&](int, int kx, Cx<T> wn) {
-                                 stc(wmain + (size_t)kx * MH, wn);
-                                 stc(buf_w + kx * TC + c, wn);
-                               },
-                               [&](int, int kx) { return ldc(buf_h + kx * TC + c); },
-                               [&](int, int kx) { return ldc(buf_w + kx * TC + c); });
-        __syncthreads();  // buf_h has been consumed and becomes the exchange buffer
-      }
+      Cx<T>* wmain = a.wmain + b * plane + q;
+      Cx<T>* hmain = a.hmain + b * plane + q;
+      rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
+                             [&](int, int kx, Cx<T> h) { if (a.store_h) stc(hmain + (size_t)kx * MH, h); },
+                             [&](int, int kx, Cx<T> wn) {
+                               stc(wmain + (size_t)kx * MH, wn);
+                               stc(buf_w + kx * TC + c, wn);
+                             },
+                             [&](int, int kx) { return ldc(buf_h + kx * TC + c); },
+                             [&](int, int kx) { return ldc(buf_w + kx * TC + c); },
+                             [&](int, int kx) {
+                               return a.ctrl_main ? ldc(a.ctrl_main + (size_t)kx * MH + q) : mk<T>((T)0, (T)0);
+                             });
+      __syncthreads();  // buf_h has been consumed and becomes the exchange buffer
     }
 
     auto load_w = [&](int, int kx) { return ldc(buf_w + kx * TC + c); };
@@ -240,14 +202,11 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     col_field_pair<1, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
     __syncthreads();  // every thread has read its omega_hat for the second pair and left the last exchange
     if (tid == 0 && has_next) {
-      if (TSTORE) bulk_wait_read0();  // the TMA stores have read buf_adv / buf_w
       fence_proxy_async();
-      if (STAGES == 2 && !next_masked) issue(buf_adv, &m_adv, bar + 0, next);
       if (use_h) issue(buf_h, &m_h, bar + 1, next);
       issue(buf_w, &m_w, bar + 2, next);
     }
   }
-  if (TSTORE && tid == 0) bulk_wait0();  // all TMA stores have landed before the CTA retires
 }
 
 }  // namespace kf

@@ -33,6 +33,8 @@ template <typename T> struct StageArgs {
   Cx<T>* hmain;        // [Bc][N][M/2]
   Cx<T>* hnyq;         // [Bc][N]
   const Cx<T>* G;      // [Bc][M/2+1]  forcing + control row (kx = 0)
+  const Cx<T>* ctrl_main;  // [N][M/2] dense control spectrum shared by all environments (general control_field of
+  const Cx<T>* ctrl_nyq;   // [N]      solve(), kolmogorov.py:259-272); NULL = none (the env path: row kx = 0 only)
   Cx<T>* advx;         // [Bc][N][M/2] packed x-space advection
   Cx<L2>* fa;          // [Bc][N][M/2] lanes (u_hat, gx_hat) in x-space
   Cx<L2>* fb;          // [Bc][N][M/2] lanes (v_hat, gy_hat) in x-space
@@ -123,6 +125,7 @@ __device__ __forceinline__ void nyquist_column_update(const StageArgs<T>& a, con
     Cx<T> h = mk<T>((T)0.5 * d.y, (T)-0.5 * d.x);
     if (a.dealias) h = mk<T>((T)0, (T)0);  // ky = M/2 >= km always
     if (kx == 0) h = h + ldc(G + MH);
+    if (a.ctrl_nyq) h = h + ldc(a.ctrl_nyq + kx);
     if (use_h) h = h + a.beta * ldc(hnyq + kx);
     if (a.store_h) stc(hnyq + kx, h);
     const T p = (T)(kx < N / 2 ? kx : kx - N);
@@ -193,11 +196,15 @@ __device__ __forceinline__ void col_field_pair(const StageArgs<T>& a, LoadW load
 
 // RK accumulate + Crank-Nicolson update of one column (S:53-56, K:209-220): v[] holds the forward
 // x-transform of the advection column (column 0 already unpacked); load_h / load_w fetch the old
-// h / omega_hat of row kx, store_h / store_w dispose of the new ones.  Returns the new omega_hat in w[].
-template <typename T, class P, class Args, class StoreH, class StoreW, class LoadH, class LoadW>
+// h / omega_hat of row kx, store_h / store_w dispose of the new ones, extra(m, kx) is a further source term added
+// after the mask (the dense control spectrum; callers without one pass zero_extra).  Returns the new omega_hat in w[].
+template <typename T> struct ZeroExtra {
+  __device__ __forceinline__ Cx<T> operator()(int, int) const { return mk<T>((T)0, (T)0); }
+};
+template <typename T, class P, class Args, class StoreH, class StoreW, class LoadH, class LoadW, class Extra>
 __device__ __forceinline__ void rk_update_column(const Args& a, const Cx<T>* v, Cx<T>* w, Cx<T> g0, bool use_h,
                                                  int t, int q, StoreH store_h, StoreW store_w, LoadH load_h,
-                                                 LoadW load_w) {
+                                                 LoadW load_w, Extra extra) {
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
   constexpr int kn = (N / 2) * 2 / 3, km = ((MH + 1) * 2) / 3;
   const T tf = (T)t, qf = (T)q;
@@ -207,6 +214,7 @@ __device__ __forceinline__ void rk_update_column(const Args& a, const Cx<T>* v, 
     Cx<T> h = v[m];
     if (a.dealias && ((kx >= kn && kx < 2 * kn) || q >= km)) h = mk<T>((T)0, (T)0);
     if (m == 0) h = h + g0;  // g0 is zero except on row kx = 0 (t == 0)
+    h = h + extra(m, kx);
     if (use_h) h = h + a.beta * load_h(m, kx);
     store_h(m, kx, h);
     const T p = wave_p<T, P>(tf, m);
@@ -288,7 +296,10 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB) col_kernel(StageArgs<T> a) {
                            [&](int, int kx, Cx<T> h) { if (a.store_h) stc(hmain + (size_t)kx * MH, h); },
                            [&](int, int kx, Cx<T> wn) { stc(wmain + (size_t)kx * MH, wn); },
                            [&](int, int kx) { return ldc(hmain + (size_t)kx * MH); },
-                           [&](int, int kx) { return ldc(wmain + (size_t)kx * MH); });
+                           [&](int, int kx) { return ldc(wmain + (size_t)kx * MH); },
+                           [&](int, int kx) {
+                             return a.ctrl_main ? ldc(a.ctrl_main + (size_t)kx * MH + q) : mk<T>((T)0, (T)0);
+                           });
   } else {
 #pragma unroll
     for (int m = 0; m < E; ++m) w[m] = ldc(wmain + (size_t)(t + TPF * m) * MH);

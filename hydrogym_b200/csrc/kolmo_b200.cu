@@ -65,6 +65,7 @@ struct Ops {
   void (*finalize)(const struct Ctx&, int nsnap, void* mean_tke, int* nonfinite, cudaStream_t);
   void (*import_)(const struct Ctx&, int nb, const void* user, size_t user_env, cudaStream_t);
   void (*export_)(const struct Ctx&, int nb, void* user, size_t user_env, cudaStream_t);
+  void (*export_h)(const struct Ctx&, int nb, void* user, size_t user_env, cudaStream_t);  // the RK register h
   void (*forcing)(const struct Ctx&, int nb, const void* actions, cudaStream_t);
 };
 
@@ -84,7 +85,11 @@ struct Ctx {
   int* d_nonf = nullptr;
   size_t bytes = 0;
   long long launches = 0;
+  mutable cudaError_t launch_err = cudaSuccess;  // first failed cudaLaunchKernelEx of a stage kernel
   bool have_constants = false;
+  // dense control spectrum (general control_field of RungeKuttaCrankNicolson.solve): [N][MH] + [N]; owner = lane 0
+  void *ctrl_main = nullptr, *ctrl_nyq = nullptr;
+  bool ctrl_on = false, ctrl_owner = false;
   // TMA column kernel: tensor maps over advx / hmain / wmain and the persistent grid size
   CUtensorMap tm_adv, tm_h, tm_w;
   bool use_tma = false;
@@ -105,7 +110,7 @@ struct Ctx {
 
 // TC: columns per column-kernel CTA; GROUPS: FFT groups per row-kernel CTA;
 // CB / RB: __launch_bounds__ min-blocks (register caps) of the column / row kernels.
-template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int TB = 1, int ST = 1, bool TS = false> struct Impl {
+template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int TB = 1> struct Impl {
   using C = kf::Cx<T>;
   static constexpr int N = P::L, MH = N / 2;
   using C2 = kf::Cx<typename kf::PairOf<T>::type>;  // lane-paired complex (two transforms per element)
@@ -133,6 +138,8 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     kf::StageArgs<T> a;
     a.wmain = (C*)c.wmain; a.wnyq = (C*)c.wnyq; a.hmain = (C*)c.hmain; a.hnyq = (C*)c.hnyq;
     a.G = (const C*)c.G; a.advx = (C*)c.advx;
+    a.ctrl_main = c.ctrl_on ? (const C*)c.ctrl_main : nullptr;
+    a.ctrl_nyq = c.ctrl_on ? (const C*)c.ctrl_nyq : nullptr;
     a.fa = (C2*)c.fld; a.fb = a.fa + (size_t)c.chunk * c.plane;
     a.tw = (const C*)c.tw;
     a.beta = 0; a.gdt = 0; a.munu = 0;
@@ -158,7 +165,8 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = at; lc.numAttrs = c.pdl ? 1 : 0;
-    cudaLaunchKernelEx(&lc, kernel, kargs...);
+    const cudaError_t e = cudaLaunchKernelEx(&lc, kernel, kargs...);
+    if (e != cudaSuccess && c.launch_err == cudaSuccess) c.launch_err = e;  // reported by run_rk_steps / drive
   }
   static void row(const Ctx& c, int nb, cudaStream_t s) {
     kf::StageArgs<T> a = args(c);
@@ -189,6 +197,9 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
   static void export_(const Ctx& c, int nb, void* user, size_t user_env, cudaStream_t s) {
     kf::export_kernel<T><<<dim3(32, nb), 256, 0, s>>>((C*)user, user_env, (const C*)c.wmain, (const C*)c.wnyq, N, MH);
   }
+  static void export_h(const Ctx& c, int nb, void* user, size_t user_env, cudaStream_t s) {
+    kf::export_kernel<T><<<dim3(32, nb), 256, 0, s>>>((C*)user, user_env, (const C*)c.hmain, (const C*)c.hnyq, N, MH);
+  }
   static void forcing(const Ctx& c, int nb, const void* actions, cudaStream_t s) {
     kf::forcing_row_kernel<T><<<dim3((MH + 1 + 127) / 128, nb), 128, 0, s>>>(
         (C*)c.G, (const C*)c.F, (const C*)c.C, (const T*)actions, (T)c.cfg.min_action, (T)c.cfg.max_action, MH + 1);
@@ -199,7 +210,7 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     a.beta = (T)st.beta; a.gdt = (T)st.gdt; a.munu = (T)st.munu; a.store_h = st.store_h;
     const int ntiles = nb * (MH / TC);
     const int grid = ntiles < c.tma_ctas ? ntiles : c.tma_ctas;
-    launch_stage(c, kf::col_tma_kernel<T, P, TC, TB, ST, TS>, dim3(grid), P::TPF * TC, kf::ColTmaSmem<T, P, TC, ST>::bytes(),
+    launch_stage(c, kf::col_tma_kernel<T, P, TC, TB>, dim3(grid), P::TPF * TC, kf::ColTmaSmem<T, P, TC>::bytes(),
                  s, a, c.tm_adv, c.tm_h, c.tm_w, ntiles);
   }
   static Ops make() {
@@ -208,7 +219,7 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     o.tc = TC; o.col_threads = P::TPF * TC; o.row_groups = GROUPS; o.row_threads = P::TPF * GROUPS;
     o.col_smem = col_smem(); o.row_smem = row_smem();
     o.prepare = prepare; o.fill_tw = kf::fill_twiddles<P>; o.tma_setup = tma_setup; o.col_tma = col_tma; o.col = col; o.row = row; o.obs = obs; o.fields = fields; o.finalize = finalize;
-    o.import_ = import_; o.export_ = export_; o.forcing = forcing;
+    o.import_ = import_; o.export_ = export_; o.export_h = export_h; o.forcing = forcing;
     return o;
   }
 };
@@ -231,12 +242,12 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-template <typename T, class P, int TC, int GROUPS, int CB, int RB, int TB, int ST, bool TS>
-int Impl<T, P, TC, GROUPS, CB, RB, TB, ST, TS>::tma_setup(Ctx& c) {
+template <typename T, class P, int TC, int GROUPS, int CB, int RB, int TB>
+int Impl<T, P, TC, GROUPS, CB, RB, TB>::tma_setup(Ctx& c) {
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) return fail("cuTensorMapEncodeTiled is not available from this driver");
-  const size_t smem = kf::ColTmaSmem<T, P, TC, ST>::bytes();
-  auto kern = kf::col_tma_kernel<T, P, TC, TB, ST, TS>;
+  const size_t smem = kf::ColTmaSmem<T, P, TC>::bytes();
+  auto kern = kf::col_tma_kernel<T, P, TC, TB>;
   KF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0, sms = 0;
   KF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, P::TPF * TC, smem));
@@ -277,13 +288,7 @@ int Impl<T, P, TC, GROUPS, CB, RB, TB, ST, TS>::tma_setup(Ctx& c) {
 #ifndef KF_F256_TB
 #define KF_F256_TB 2
 #endif
-#ifndef KF_F256_ST
-#define KF_F256_ST 1
-#endif
-#ifndef KF_F256_TS
-#define KF_F256_TS false
-#endif
-#define KF_CFG_F256 KF_F256_TC, KF_F256_GROUPS, KF_F256_CB, KF_F256_RB, KF_F256_TB, KF_F256_ST, KF_F256_TS
+#define KF_CFG_F256 KF_F256_TC, KF_F256_GROUPS, KF_F256_CB, KF_F256_RB, KF_F256_TB
 // fp64: 16 elements per thread (one exchange fewer per transform than 8) beats the lower register pressure of 8:
 // 256^2 row kernel 242 -> 186 us, column kernel 300 -> 278 us per launch (256 envs)
 #ifndef KF_D256_RB
@@ -435,6 +440,12 @@ int run_rk_steps(Ctx* const* L, const int* nb, const cudaStream_t* ls, int nl, i
     }
   }
   KF_CUDA(cudaGetLastError());
+  for (int l = 0; l < nl; ++l)
+    if (L[l]->launch_err != cudaSuccess) {
+      const cudaError_t e = L[l]->launch_err;
+      L[l]->launch_err = cudaSuccess;
+      return fail(std::string("stage kernel launch: ") + cudaGetErrorString(e));
+    }
   return 0;
 }
 
@@ -540,7 +551,8 @@ void free_all(Ctx& c) {
   if (c.ev_fork) cudaEventDestroy(c.ev_fork);
   if (c.ev_join) cudaEventDestroy(c.ev_join);
   void* ptrs[] = {c.wmain, c.wnyq, c.hmain, c.hnyq, c.G, c.fld, c.advx, c.tw, c.F, c.C,
-                  c.acc, c.d_omega, c.d_act, c.d_obs, c.d_tke, c.d_nonf};
+                  c.acc, c.d_omega, c.d_act, c.d_obs, c.d_tke, c.d_nonf, c.ctrl_owner ? c.ctrl_main : nullptr,
+                  c.ctrl_owner ? c.ctrl_nyq : nullptr};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (c.graph) cudaGraphExecDestroy(c.graph);
@@ -814,44 +826,124 @@ int kf_step_host(kf_handle h, void* omega_hat_host, const void* actions_host, vo
 
 extern "C" {
 
-// Measurement aid for bench.py: time `reps` back-to-back launches of the column kernel
-// (sub-stage `stage`, epilogue + prologue) and of the row kernel on the current chunk
-// workspace with CUDA events on `stream`.  The workspace contents are advanced as in a
-// real run (each launch is a genuine sub-stage), so call it on scratch state only.
+// Measurement aid for bench.py: per-launch duration of the column kernel and of the row kernel measured INSIDE the
+// real launch sequence of a sub-stage (row, column, row, column, ... on one lane's chunk workspace, one CUDA event
+// between any two launches), so each kernel finds the caches in the state its predecessor leaves them in.  The
+// workspace contents are advanced as in a real run (each launch is a genuine sub-stage): scratch state only.
 int kf_profile_kernels(kf_handle h, int reps, float* ms_col, float* ms_row, void* stream) {
-  if (!h || reps < 1) return fail("kf_profile_kernels: bad argument");
+  if (!h || reps < 1 || reps > 4096) return fail("kf_profile_kernels: bad argument");
   Ctx& c = h->c;
   if (!c.have_constants) return fail("kf_set_constants has not been called");
   DeviceGuard guard(c.cfg.device);
   cudaStream_t s = (cudaStream_t)stream;
-  cudaEvent_t e0, e1, e2;
-  KF_CUDA(cudaEventCreate(&e0));
-  KF_CUDA(cudaEventCreate(&e1));
-  KF_CUDA(cudaEventCreate(&e2));
+  std::vector<cudaEvent_t> ev(2 * (size_t)reps + 1);
+  for (auto& e : ev) KF_CUDA(cudaEventCreate(&e));
   const int nb = c.chunk;
+  auto col = [&](int k) {
+    if (c.use_tma) c.ops->col_tma(c, nb, stage_of(c, k), s);
+    else c.ops->col(c, nb, stage_of(c, k), kf::kColStage, s);
+  };
   c.ops->forcing(c, nb, nullptr, s);
   for (int i = 0; i < 3; ++i) {  // warm-up
     c.ops->row(c, nb, s);
-    c.ops->col(c, nb, stage_of(c, 1), kf::kColStage, s);
+    col(1);
   }
-  KF_CUDA(cudaEventRecord(e0, s));
   for (int i = 0; i < reps; ++i) {
-    if (c.use_tma) c.ops->col_tma(c, nb, stage_of(c, 1 + i % 3), s);  // sub-stages that move all 9C
-    else c.ops->col(c, nb, stage_of(c, 1 + i % 3), kf::kColStage, s);
+    KF_CUDA(cudaEventRecord(ev[2 * i], s));
+    c.ops->row(c, nb, s);
+    KF_CUDA(cudaEventRecord(ev[2 * i + 1], s));
+    col(1 + i % 3);  // sub-stages 1..3 move all 9C (stage 0 does not read h, stage 4 does not write it)
   }
-  KF_CUDA(cudaEventRecord(e1, s));
-  for (int i = 0; i < reps; ++i) c.ops->row(c, nb, s);
-  KF_CUDA(cudaEventRecord(e2, s));
-  KF_CUDA(cudaEventSynchronize(e2));
-  float a = 0, b = 0;
-  KF_CUDA(cudaEventElapsedTime(&a, e0, e1));
-  KF_CUDA(cudaEventElapsedTime(&b, e1, e2));
-  if (ms_col) *ms_col = a / reps;
-  if (ms_row) *ms_row = b / reps;
+  KF_CUDA(cudaEventRecord(ev[2 * reps], s));
+  KF_CUDA(cudaEventSynchronize(ev[2 * reps]));
+  double tr = 0, tc = 0;
+  for (int i = 0; i < reps; ++i) {
+    float a = 0, b = 0;
+    KF_CUDA(cudaEventElapsedTime(&a, ev[2 * i], ev[2 * i + 1]));
+    KF_CUDA(cudaEventElapsedTime(&b, ev[2 * i + 1], ev[2 * i + 2]));
+    tr += a;
+    tc += b;
+  }
+  if (ms_col) *ms_col = (float)(tc / reps);
+  if (ms_row) *ms_row = (float)(tr / reps);
   c.launches += 2LL * reps + 7;
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
-  cudaEventDestroy(e2);
+  for (auto& e : ev) cudaEventDestroy(e);
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Dense control spectrum for the general control_field of RungeKuttaCrankNicolson.solve (base.py:104-105,
+// kolmogorov.py:259-272): control_hat_host [N][M/2+1] complex in the handle's dtype, added to the nonlinear term of
+// every environment in every sub-stage after the (optional) 2/3 mask; NULL removes it.  Synchronous.
+int kf_set_control_field(kf_handle h, const void* control_hat_host) {
+  if (!h) return fail("kf_set_control_field: null handle");
+  Ctx& c = h->c;
+  DeviceGuard guard(c.cfg.device);
+  KF_CUDA(cudaDeviceSynchronize());
+  for (Ctx* l : {&c, c.lane2}) {  // captured graphs hold the old kernel arguments
+    if (l && l->graph) {
+      cudaGraphExecDestroy(l->graph);
+      l->graph = nullptr;
+    }
+  }
+  if (!control_hat_host) {
+    for (Ctx* l : {&c, c.lane2})
+      if (l) l->ctrl_on = false;
+    return 0;
+  }
+  const size_t el = c.ops->elem;
+  const int N = c.N, MH = c.MH;
+  if (!c.ctrl_main) {
+    if (int rc = dev_alloc(c, &c.ctrl_main, el * (size_t)N * MH)) return rc;
+    if (int rc = dev_alloc(c, &c.ctrl_nyq, el * (size_t)N)) return rc;
+    c.ctrl_owner = true;
+  }
+  // split the user layout [N][MH+1] into main [N][MH] + nyq [N] on the host side of the copy (strided 2-D copies)
+  KF_CUDA(cudaMemcpy2D(c.ctrl_main, el * MH, control_hat_host, el * (MH + 1), el * MH, N, cudaMemcpyHostToDevice));
+  KF_CUDA(cudaMemcpy2D(c.ctrl_nyq, el, (const char*)control_hat_host + el * MH, el * (MH + 1), el, N,
+                       cudaMemcpyHostToDevice));
+  for (Ctx* l : {&c, c.lane2}) {
+    if (!l) continue;
+    l->ctrl_main = c.ctrl_main;
+    l->ctrl_nyq = c.ctrl_nyq;
+    l->ctrl_on = true;
+  }
+  return 0;
+}
+
+// PseudoSpectralNavierStokes2D.nonlinear_terms (kolmogorov.py:222-257) of omega_hat_dev [B][N][M/2+1]:
+// out_dev [B][N][M/2+1] = dealiasing(rfftn(-(grad_x*u + grad_y*v))) + forcing_term + control, the control being
+// sum_m clip(a_m) C_m from actions_dev [B][4] (NULL = none) plus the dense spectrum of kf_set_control_field if one is
+// set.  Runs one sub-stage's kernels (x-space fields, row kernel, forward column pass with beta = gamma = mu = 0, which
+// leaves omega_hat untouched and the term in the RK register) and exports the register.  Scratches the workspace.
+int kf_nonlinear_terms(kf_handle h, const void* omega_hat_dev, const void* actions_dev, void* out_dev, void* stream) {
+  if (!h || !omega_hat_dev || !out_dev) return fail("kf_nonlinear_terms: null argument");
+  Ctx& c = h->c;
+  if (!c.have_constants) return fail("kf_set_constants has not been called");
+  DeviceGuard guard(c.cfg.device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t el = c.ops->elem, real = el / 2;
+  const int B = c.cfg.B;
+  const size_t user_env = (size_t)c.N * (c.MH + 1);
+  Stage st;
+  st.beta = 0.0; st.gdt = 0.0; st.munu = 0.0; st.store_h = 1;
+  for (int b0 = 0; b0 < B; b0 += c.chunk) {
+    const int nb = (B - b0 < c.chunk) ? (B - b0) : c.chunk;
+    c.ops->import_(c, nb, (const char*)omega_hat_dev + el * user_env * b0, user_env, s);
+    c.ops->forcing(c, nb, actions_dev ? (const char*)actions_dev + real * 4 * b0 : nullptr, s);
+    c.ops->col(c, nb, st, kf::kColInit, s);
+    c.ops->row(c, nb, s);
+    if (c.use_tma) c.ops->col_tma(c, nb, st, s);
+    else c.ops->col(c, nb, st, kf::kColStage, s);
+    c.ops->export_h(c, nb, (char*)out_dev + el * user_env * b0, user_env, s);
+    c.launches += 6;
+  }
+  KF_CUDA(cudaGetLastError());
+  if (c.launch_err != cudaSuccess) {
+    const cudaError_t e = c.launch_err;
+    c.launch_err = cudaSuccess;
+    return fail(std::string("stage kernel launch: ") + cudaGetErrorString(e));
+  }
   return 0;
 }
 

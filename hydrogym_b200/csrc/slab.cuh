@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
                            [&](int, int kx, Cx<T> h) { if (live) stc(hrow + kx, h); },
                            [&](int, int kx, Cx<T> wv) { if (live) stc(wrow + kx, wv); },
                            [&](int, int kx) { return ldc(hrow + kx); },
-                           [&](int, int kx) { return ldc(wrow + kx); });
+                           [&](int, int kx) { return ldc(wrow + kx); }, ZeroExtra<T>());
   } else if constexpr (SPECIAL) {
 #pragma unroll
     for (int m = 0; m < E; ++m) {

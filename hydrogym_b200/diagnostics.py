@@ -57,16 +57,50 @@ def compute_velocity_mode(uhat, vhat, kx, ky, n, m):
     return torch.sqrt((uhat[..., kx % n, ky % m].abs() ** 2 + vhat[..., kx % n, ky % m].abs() ** 2) / float(n * m) ** 2)
 
 
-def _velocity(omega_hat, Re=1000.0):
-    """(u, v) physical fields (B, N, N) of omega_hat (B, N, Mh) or (N, Mh) through the row-FFT kernels."""
+_STEPPERS = {}
+
+
+def _stepper(N, B, dtype, device):
+    """One cached ``KolmogorovStepper`` per (N, B, dtype, device): the diagnostics only use its x-space-field, row
+    and reduction kernels, so the workspace, twiddle tables and TMA descriptors are built once, not per call."""
     from .solver import KolmogorovStepper
+    key = (int(N), int(B), dtype, str(device))
+    st = _STEPPERS.get(key)
+    if st is None:
+        if len(_STEPPERS) >= 8:  # bounded: drop the oldest workspace
+            _STEPPERS.pop(next(iter(_STEPPERS))).close()
+        st = _STEPPERS[key] = KolmogorovStepper(grid_size=(N, N), num_envs=B, dtype=dtype, device=device,
+                                                n_inner=1, n_outer=1)
+    return st
+
+
+def clear_cache():
+    """Free the cached diagnostic workspaces."""
+    while _STEPPERS:
+        _STEPPERS.popitem()[1].close()
+
+
+def _velocity(omega_hat):
+    """(u, v) physical fields (B, N, N) of omega_hat (B, N, Mh) or (N, Mh) through the row-FFT kernels."""
     w = omega_hat[None] if omega_hat.dim() == 2 else omega_hat
     rd = torch.float32 if w.dtype == torch.complex64 else torch.float64
-    st = KolmogorovStepper(grid_size=(w.shape[1], w.shape[1]), Re=Re, num_envs=w.shape[0], dtype=rd, device=w.device,
-                           n_inner=1, n_outer=1)
-    uv = st.physical_fields(w.contiguous(), 2)
-    st.close()
+    uv = _stepper(w.shape[1], w.shape[0], rd, w.device).physical_fields(w.contiguous(), 2)
     return uv[0], uv[1]
+
+
+def _strain(omega_hat, nu, want_eps, want_div):
+    u, v = _velocity(omega_hat)
+    B, N = int(u.shape[0]), int(u.shape[1])
+    eps = torch.empty((B,), dtype=torch.float64, device=u.device) if want_eps else None
+    div = torch.empty_like(u) if want_div else None
+    lib = _lib.load()
+    with torch.cuda.device(u.device):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(u.device).cuda_stream)
+        _lib.check(lib.kf_strain_diagnostics(
+            _lib.KF_F32 if u.dtype == torch.float32 else _lib.KF_F64, N, B, float(nu), ctypes.c_void_p(u.data_ptr()),
+            ctypes.c_void_p(v.data_ptr()), ctypes.c_void_p(eps.data_ptr() if want_eps else 0),
+            ctypes.c_void_p(div.data_ptr() if want_div else 0), stream), "kf_strain_diagnostics")
+    return eps, div
 
 
 def compute_real_velocity_point(omega_hat, x_idx, y_idx):
@@ -78,18 +112,15 @@ def compute_real_velocity_point(omega_hat, x_idx, y_idx):
 
 def compute_energy_dissipation(omega_hat, nu):
     """utils.py:145-172: 2 nu <S_ij S_ij> with the reference's finite differences in INDEX units
-    (jnp.gradient, unit spacing, one-sided at the edges), summed and divided by 4 pi^2."""
-    u, v = _velocity(omega_hat)
-    du_dx, du_dy = torch.gradient(u, dim=(1, 2))
-    dv_dx, dv_dy = torch.gradient(v, dim=(1, 2))
-    eps = (2 * nu * (du_dx ** 2 + dv_dy ** 2 + (du_dy + dv_dx) ** 2)).sum(dim=(1, 2)) / (4 * torch.pi ** 2)
+    (jnp.gradient, unit spacing, one-sided at the edges), summed and divided by 4 pi^2 -- one CUDA reduction
+    (``kf_strain_diagnostics``) over the physical velocity fields.  Returns float64."""
+    eps, _ = _strain(omega_hat, nu, True, False)
     return eps[0] if omega_hat.dim() == 2 else eps
 
 
 def compute_divergence(omega_hat):
     """utils.py:213-229: du/dx + dv/dy with the same index-unit finite differences (not spectrally exact)."""
-    u, v = _velocity(omega_hat)
-    div = torch.gradient(u, dim=1)[0] + torch.gradient(v, dim=2)[0]
+    _, div = _strain(omega_hat, 0.0, False, True)
     return div[0] if omega_hat.dim() == 2 else div
 
 
@@ -97,13 +128,9 @@ def compute_tke(omega_hat):
     """utils.py:175-194: turbulent kinetic energy sum(0.5 (|u - mean u|^2 + |v - mean v|^2)) / n^2 of one state (N, Mh)
     or a batch (B, N, Mh), through the fused reward / observation kernel (``kf_reward_obs`` on a one-snapshot
     trajectory: c2r of u_hat, v_hat, fp64 warp-shuffle sums)."""
-    from .solver import KolmogorovStepper
     w = omega_hat[None] if omega_hat.dim() == 2 else omega_hat
     rd = torch.float32 if w.dtype == torch.complex64 else torch.float64
-    st = KolmogorovStepper(grid_size=(w.shape[1], w.shape[1]), num_envs=w.shape[0], dtype=rd, device=w.device,
-                           n_inner=1, n_outer=1)
-    _, tke, _ = st.reward_obs(w[:, None].contiguous())
-    st.close()
+    _, tke, _ = _stepper(w.shape[1], w.shape[0], rd, w.device).reward_obs(w[:, None].contiguous())
     return tke[0] if omega_hat.dim() == 2 else tke
 
 

@@ -43,6 +43,7 @@ class FlowConfig:
         self.obs_size = config.get("obs_size", self.DEFAULT_OBS_SIZE)
         if self.grid_size[0] != self.grid_size[1]:
             raise ValueError("hydrogym_b200 supports square grids only")
+        constants.check_domain(self.domain_x, self.domain_y)
         if self.grid_size[0] % self.obs_size != 0:
             raise ValueError("obs_size must divide the grid size")
         self.vorticity = None
@@ -167,7 +168,8 @@ class KolmogorovFlow:
         self.n_inner, self.n_outer = constants.step_counts(
             float(default.dt), float(default.action_time), int(default.save_time))
         from ..solvers.base import PseudoSpectralNavierStokes2D, RungeKuttaCrankNicolson  # noqa: WPS433
-        self.equation = PseudoSpectralNavierStokes2D(self.flow)
+        self.equation = PseudoSpectralNavierStokes2D(self.flow, dtype=self.dtype, device=self.device,
+                                                     dealias=self.dealias)
         self.integrator = RungeKuttaCrankNicolson(
             flow=self.flow, dt=float(default.dt), save_n=int(default.save_time), equation=self.equation,
             dtype=self.dtype, device=self.device, dealias=self.dealias)

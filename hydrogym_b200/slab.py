@@ -76,6 +76,7 @@ class SlabKolmogorovSolver:
         N, M = grid_size
         if N != M:
             raise ValueError("only square grids are supported")
+        constants.check_domain((0, 2 * np.pi), domain_y)
         if not torch.cuda.is_available():
             raise RuntimeError("hydrogym_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
         dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")

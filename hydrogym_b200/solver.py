@@ -31,6 +31,7 @@ class KolmogorovStepper:
         N, M = grid_size
         if N != M:
             raise ValueError("only square grids are supported")
+        constants.check_domain(domain_x, domain_y)
         if not torch.cuda.is_available():
             raise RuntimeError("hydrogym_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -67,6 +68,20 @@ class KolmogorovStepper:
         self.control_rows = np.ascontiguousarray(np.asarray(rows).astype(np_c))
         _lib.check(self._lib.kf_set_constants(self._h, self.forcing_row.ctypes.data_as(ctypes.c_void_p),
                                               self.control_rows.ctypes.data_as(ctypes.c_void_p)), "kf_set_constants")
+
+    def set_control_field(self, control_hat):
+        """Dense control spectrum (N, Mh) -- ``control_term`` of an arbitrary ``(cfx, cfy)`` field (K:259-272) --
+        added to the nonlinear term of every environment in every sub-stage; ``None`` removes it."""
+        if control_hat is None:
+            _lib.check(self._lib.kf_set_control_field(self._h, ctypes.c_void_p(0)), "kf_set_control_field")
+            return
+        np_c = np.complex64 if self.dtype == torch.float32 else np.complex128
+        if isinstance(control_hat, torch.Tensor):
+            control_hat = control_hat.detach().cpu().numpy()
+        arr = np.ascontiguousarray(np.asarray(control_hat).astype(np_c))
+        if arr.shape != (self.N, self.Mh):
+            raise ValueError(f"control_hat must be {(self.N, self.Mh)}, got {arr.shape}")
+        _lib.check(self._lib.kf_set_control_field(self._h, arr.ctypes.data_as(ctypes.c_void_p)), "kf_set_control_field")
 
     # -- helpers -------------------------------------------------------------
     def close(self):
@@ -174,6 +189,17 @@ class KolmogorovStepper:
                        "kf_physical_fields")
         return out
 
+    def nonlinear_terms(self, omega_hat, actions=None):
+        """``PseudoSpectralNavierStokes2D.nonlinear_terms`` (K:222-257) of (B, N, Mh): advection + forcing + control
+        (``actions`` (B, 4) through the control rows, plus the dense field of ``set_control_field`` if set)."""
+        self._check_state(omega_hat)
+        actions = self._check_actions(actions)
+        out = torch.empty_like(omega_hat)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.kf_nonlinear_terms(self._h, _ptr(omega_hat), _ptr(actions), _ptr(out), self._stream()),
+                       "kf_nonlinear_terms")
+        return out
+
     def profile_kernels(self, reps=20):
         """(ms per column-kernel launch, ms per row-kernel launch) on scratch workspace data."""
         a, b = ctypes.c_float(0), ctypes.c_float(0)
@@ -186,3 +212,32 @@ class KolmogorovStepper:
         """``kf_step_host``: all arguments are HOST tensors (pinned for speed); synchronous, in place."""
         _lib.check(self._lib.kf_step_host(self._h, _ptr(omega_hat_host), _ptr(actions_host), _ptr(obs_host),
                                           _ptr(tke_host), _ptr(nonf_host)), "kf_step_host")
+
+
+def _spectral_pointwise(name, omega_hat, nu, *extra):
+    if not isinstance(omega_hat, torch.Tensor) or not omega_hat.is_cuda:
+        raise ValueError("omega_hat must be a CUDA tensor (hydrogym_b200 has no CPU fallback)")
+    if omega_hat.dtype not in (torch.complex64, torch.complex128):
+        raise ValueError("omega_hat must be complex64 or complex128")
+    N, Mh = omega_hat.shape[-2:]
+    if Mh != N // 2 + 1:
+        raise ValueError("omega_hat must be (..., N, N//2+1)")
+    w = omega_hat.contiguous()
+    out = torch.empty_like(w)
+    B = w.numel() // (N * Mh)
+    lib = _lib.load()
+    with torch.cuda.device(w.device):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(w.device).cuda_stream)
+        dt = _lib.KF_F32 if w.dtype == torch.complex64 else _lib.KF_F64
+        _lib.check(getattr(lib, name)(dt, int(N), int(B), float(nu), *extra, _ptr(w), _ptr(out), stream), name)
+    return out
+
+
+def linear_terms(omega_hat, nu):
+    """K:209-211 on device: ``nu * (2 pi i)^2 (kx^2 + ky^2) * omega_hat`` for (..., N, N//2+1)."""
+    return _spectral_pointwise("kf_linear_terms", omega_hat, nu)
+
+
+def implicit_timestep(omega_hat, nu, time_step):
+    """K:213-220 on device: ``omega_hat / (1 - time_step * nu * (2 pi i)^2 (kx^2 + ky^2))``."""
+    return _spectral_pointwise("kf_implicit_timestep", omega_hat, nu, float(time_step))

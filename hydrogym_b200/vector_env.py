@@ -50,13 +50,18 @@ class KolmogorovVectorEnv:
         self._stepper._check_state(omega_hat)
         self.omega_hat = omega_hat.clone()
         self.time = torch.zeros((self.num_envs,), dtype=torch.int64, device=self.device)
+        self._cache_reset()
+
+    def _cache_reset(self):
+        """Post-reset (obs, omega_hat, trajectory) of one environment -- what time-limit truncation resets to."""
+        obs, final, traj = self.env._reset_single(self.params)
+        self._reset_obs, self._reset_omega, self._reset_traj = obs, final, traj
 
     def reset(self, seed=None, options=None):
         obs, state = self.env.reset_env(seed, self.params, num_envs=self.num_envs)
         self.omega_hat, self.time = state.omega_hat, state.time
         self.trajectory = state.trajectory if self.keep_trajectory else None
-        self._reset_obs = obs[0].clone()
-        self._reset_omega = state.omega_hat[0].clone()
+        self._cache_reset()
         return obs, {}
 
     def step(self, actions):
@@ -72,12 +77,15 @@ class KolmogorovVectorEnv:
         reward = -(p.reward_alpha * tke + actions.abs().sum(dim=-1))
         truncated = self.time >= p.max_episode_steps
         terminated = torch.zeros_like(truncated)
-        info = {"mean_tke": tke, "nonfinite": nonf}
-        if hasattr(self, "_reset_omega") and bool(truncated.any()):
-            info["final_observation"] = obs.clone()
-            self.omega_hat[truncated] = self._reset_omega
-            obs = torch.where(truncated[:, None], self._reset_obs.expand_as(obs), obs)
-            self.time = torch.where(truncated, torch.zeros_like(self.time), self.time)
+        # gymnax-style auto-reset, leaf-wise select without a host sync: truncated environments take
+        # the cached post-reset state, observation and trajectory; info["final_observation"] keeps the step's own
+        info = {"mean_tke": tke, "nonfinite": nonf, "final_observation": obs}
+        sel = truncated[:, None, None]
+        self.omega_hat = torch.where(sel, self._reset_omega.expand_as(self.omega_hat), self.omega_hat)
+        if self.trajectory is not None:
+            self.trajectory = torch.where(sel[..., None], self._reset_traj.expand_as(self.trajectory), self.trajectory)
+        obs = torch.where(truncated[:, None], self._reset_obs.expand_as(obs), obs)
+        self.time = torch.where(truncated, torch.zeros_like(self.time), self.time)
         return obs, reward, terminated, truncated, info
 
     def close(self):

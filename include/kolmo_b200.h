@@ -87,9 +87,36 @@ int kf_step(kf_handle h, void* omega_hat_dev, const void* actions_dev, void* tra
 int kf_step_host(kf_handle h, void* omega_hat_host, const void* actions_host, void* obs_host,
                  void* mean_tke_host, int* nonfinite_host);
 
-/* Measurement aid: average duration (ms, CUDA events on `stream`) of `reps` back-to-back
- * launches of the column kernel and of the row kernel on the chunk workspace.  Scratches
- * the workspace; synchronous. */
+/* Solver surface the reference documents next to the env (docs/docs/api/jax/envs/kolmogorov.md):
+ *
+ * kf_set_control_field: the general control_field of RungeKuttaCrankNicolson.solve (base.py:82-116) --
+ * control_hat_host [N][M/2+1] complex (host, handle's dtype) is control_term() of kolmogorov.py:259-272 for an
+ * arbitrary (cfx(x,y), cfy(x,y)); it is added to the nonlinear term of every environment in every RK sub-stage
+ * (base.py:53, kolmogorov.py:252-257) until cleared with NULL.  The env path does not need it (its control field is
+ * x-independent: row kx = 0 only, carried by actions x control_rows).  Synchronous.
+ *
+ * kf_nonlinear_terms: PseudoSpectralNavierStokes2D.nonlinear_terms (kolmogorov.py:222-257) of omega_hat_dev
+ * [B][N][M/2+1] -> out_dev (same shape): advection + forcing + control (actions_dev [B][4] or NULL, plus the dense
+ * field if set).  Scratches the workspace. */
+int kf_set_control_field(kf_handle h, const void* control_hat_host);
+int kf_nonlinear_terms(kf_handle h, const void* omega_hat_dev, const void* actions_dev, void* out_dev, void* stream);
+
+/* linear_terms (kolmogorov.py:209-211) and implicit_timestep (kolmogorov.py:213-220) of omega_hat_dev [B][N][N/2+1]
+ * -> out_dev (may alias the input); no handle needed. */
+int kf_linear_terms(int dtype, int N, int B, double nu, const void* omega_hat_dev, void* out_dev, void* stream);
+int kf_implicit_timestep(int dtype, int N, int B, double nu, double time_step, const void* omega_hat_dev, void* out_dev,
+                         void* stream);
+
+/* compute_energy_dissipation (utils.py:145-172) and compute_divergence (utils.py:213-229) from the physical velocity
+ * fields u_dev, v_dev [B][N][N] real (kf_physical_fields): dissipation_dev [B] double = sum 2 nu S_ij S_ij / (4 pi^2)
+ * with the reference's index-unit finite differences (jnp.gradient: central inside, one-sided at the edges);
+ * divergence_dev [B][N][N] real = du/dx + dv/dy.  Either output may be NULL. */
+int kf_strain_diagnostics(int dtype, int N, int B, double nu, const void* u_dev, const void* v_dev,
+                          double* dissipation_dev, void* divergence_dev, void* stream);
+
+/* Measurement aid: average duration (ms, CUDA events on `stream`) of the column kernel and of the row kernel
+ * measured inside `reps` repetitions of the real launch sequence (row, column, row, column, ...) on one lane's chunk
+ * workspace.  Scratches the workspace; synchronous. */
 int kf_profile_kernels(kf_handle h, int reps, float* ms_col, float* ms_row, void* stream);
 
 /* Number of kernels this handle has launched (or replayed from graphs) so far. */

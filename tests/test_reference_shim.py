@@ -283,3 +283,41 @@ np.save(sys.argv[2], np.asarray(w))
     env = orc.KolmogorovFlow(flow_config=FLOW)
     ch = env.equation.control_term(w, env._control_field(ACTION, env.default_params))
     assert rel(env.integrator.rk_steps(env.flow.initialize_state(), 100, ch), w) < 1e-12
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Equation / integrator methods on a broadband state with a GENERAL (x-dependent, cfy != 0) control field
+# (tests/golden/make_reference_solver_surface.py: the reference's own kolmogorov.py:209-272 and base.py:32-116)
+# ---------------------------------------------------------------------------------------------------------------
+SURF = np.load(os.path.join(HERE, "golden", "reference_shim_solver_surface.npz"))
+
+
+def test_oracle_equation_methods_vs_reference_source_general_control():
+    env = orc.KolmogorovFlow(flow_config=FLOW)
+    eq = env.equation
+    w, cf = SURF["w_rand"], (SURF["cfx"], SURF["cfy"])
+    ch = eq.control_term(w, cf)
+    assert rel(ch, SURF["control_term_general"]) < 1e-14
+    assert rel(eq.linear_terms(w), SURF["linear_terms_rand"]) < 1e-14
+    assert rel(eq.implicit_timestep(w, 7.5e-5), SURF["implicit_rand_mu"]) < 1e-14
+    assert rel(eq.nonlinear_terms(w, None), SURF["nonlinear_terms_rand"]) < 1e-13
+    assert rel(eq.nonlinear_terms(w, ch), SURF["nonlinear_terms_rand_ctrl"]) < 1e-13
+    assert rel(env.integrator.rk_steps(w, 10, ch), SURF["rk10_general_ctrl"]) < 1e-12
+    assert rel(env.integrator.rk_steps(w, 5, ch), SURF["step_save5_general_ctrl"]) < 1e-12
+    fin, traj = env.integrator.solve(0.05, (0, 2.0), 1, initial_state=w, control_field=cf)
+    assert traj.shape == SURF["solve_general_traj"].shape
+    assert rel(fin, SURF["solve_general_final"]) < 1e-11 and rel(traj, SURF["solve_general_traj"]) < 1e-11
+
+
+def test_product_control_spectrum_host_constant_vs_reference_source():
+    """hydrogym_b200.solvers.base.control_spectrum (the one host-side constant of a solve with a control field)."""
+    from hydrogym_b200.envs.kolmogorov import FlowConfig
+    from hydrogym_b200.solvers.base import control_spectrum
+    flow = FlowConfig(**FLOW)
+    got = control_spectrum((SURF["cfx"], SURF["cfy"]), flow)
+    assert got.shape == (64, 33) and rel(got, SURF["control_term_general"]) < 1e-14
+    assert not control_spectrum(None, flow).any()
+    # the env's own x-independent field is the special case the control rows carry
+    env = orc.KolmogorovFlow(flow_config=FLOW)
+    cf = env._control_field(ACTION, env.default_params)
+    assert rel(control_spectrum(cf, flow), REF["control_term"]) < 1e-13

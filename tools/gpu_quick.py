@@ -1,4 +1,5 @@
-"""Scratch GPU timing of the flagship configuration (not the bench)."""
+"""Quick GPU timing of named configuration presets (development aid, not the bench): ms per RK step, the 70C
+algorithmic GB/s and the isolated column / row kernel times."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -26,12 +27,19 @@ def run(N, B, dtype, steps=20, **kw):
     print(f"      col {mc*1e3:.1f} us  row {mr*1e3:.1f} us per launch (chunk {st.chunk})", flush=True)
     st.close()
 
+PRESETS = {
+    # name: list of (N, B, dtype, steps, kwargs)
+    "flagship": [(256, 256, "f32", 40, {})],
+    "configs": [(256, 256, "f32", 40, {}), (256, 256, "f64", 20, {}), (128, 1024, "f32", 20, {}),
+                (1024, 16, "f32", 10, {}), (64, 1, "f64", 200, {})],
+    "chunks": [(256, 256, "f32", 40, dict(chunk=c)) for c in (0, 16, 32, 37, 64, 74, 128)],
+    "other": [(1024, 16, "f32", 10, {}), (512, 64, "f32", 10, {}), (64, 1024, "f32", 20, {}), (128, 1024, "f64", 10, {})],
+    "nograph": [(256, 256, "f32", 40, dict(use_graph=False))],
+    "dealias": [(256, 256, "f32", 40, dict(dealias=True))],
+}
+
 if __name__ == "__main__":
-    run(256, 256, torch.float32, steps=40)
-    run(256, 256, torch.float32, steps=40, use_graph=False)
-    for ch in (16, 32, 64, 128):
-        run(256, 256, torch.float32, steps=40, chunk=ch)
-    run(256, 256, torch.float64, steps=20)
-    run(128, 1024, torch.float32, steps=20)
-    run(1024, 16, torch.float32, steps=10)
-    run(64, 1, torch.float64, steps=200)
+    # usage: tools/gpu_quick.py [preset ...]   (default: flagship); presets: see PRESETS
+    for name in (sys.argv[1:] or ["flagship"]):
+        for N, B, dt, steps, kw in PRESETS[name]:
+            run(N, B, torch.float32 if dt == "f32" else torch.float64, steps=steps, **kw)
