@@ -20,6 +20,15 @@ def rel_l2(a, b):
     return float(np.linalg.norm(a - b) / np.linalg.norm(b))
 
 
+def tail_rel_l2(got, want, frac=1e-2):
+    """Relative L2 error over the modes BELOW ``frac`` of the largest one.  From -sin x + cos y the spectrum is three
+    modes of magnitude ~2 000 over a tail below 100, so the whole-field figure mostly says that those three
+    pointwise-updated modes agree; the tail is what the FFTs and the advection product build."""
+    mask = np.abs(want) < frac * np.abs(want).max()
+    assert mask.sum() > 1000
+    return float(np.linalg.norm((got - want)[mask]) / np.linalg.norm(want[mask]))
+
+
 @pytest.mark.parametrize("dtype,tol", [("float64", 1e-9), ("float32", 1e-3)])
 def test_env_reset_and_steps_vs_reference_source(dtype, tol):
     from hydrogym_b200 import KolmogorovFlow
@@ -60,7 +69,9 @@ def test_solver_steps_vs_reference_source():
         w = w if out is None else out
         done = n
         assert rel_l2(w[0].cpu().numpy(), REF[f"zero_action_rk{n}"]) < 1e-11, n
+        assert tail_rel_l2(w[0].cpu().numpy(), REF[f"zero_action_rk{n}"]) < 1e-9, n
     assert rel_l2(w[1].cpu().numpy(), REF["action_rk100"]) < 1e-11
+    assert tail_rel_l2(w[1].cpu().numpy(), REF["action_rk100"]) < 1e-9
     st.close()
 
 
@@ -78,6 +89,8 @@ def test_single_precision_solver_steps_vs_reference_source():
         done = n
         assert rel_l2(w[0].cpu().numpy(), ref32[f"zero_action_rk{n}"]) < 1e-3, n
         assert rel_l2(w[1].cpu().numpy(), ref32[f"action_rk{n}"]) < 1e-3, n
+        if n >= 10:  # after one step the tail is still fp32 round-off of the three modes
+            assert tail_rel_l2(w[1].cpu().numpy().astype(np.complex128), ref32[f"action_rk{n}"].astype(np.complex128)) < 1e-3, n
     st.close()
 
 

@@ -170,3 +170,47 @@ def test_slab_4096_fp64_band_limited_matches_1024():
         mask = np.ones(got.shape, dtype=bool)
         mask[np.ix_(np.r_[0:kk + 1, Nl - kk:Nl], np.arange(kk + 1))] = False
         assert np.abs(got[mask]).max() < 1e-11 * np.abs(a).max() * (Nl / Ns) ** 2
+
+
+def test_slab_8192_matches_oracle_golden():
+    """ONE solver step at 8192^2 against the NumPy oracle itself (tests/golden/make_slab8192_golden.py, run in the
+    build container: fp64, reference forcing, control action ON, BROADBAND state with populated Nyquist row and
+    column -- every twiddle of the 8192-point plans and the forcing / control rows at that size are exercised).
+    The fixture holds a summary of the 537 MB result: norm, the |kx|, ky <= 32 block, 64 row-band and 64 column-band
+    norms, the Nyquist-column norm and 512 scattered entries (64 on the Nyquist row, 64 on the Nyquist column)."""
+    import os
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, os.path.join(here, "golden"))
+    import make_slab8192_golden as G
+    gold = np.load(os.path.join(here, "golden", "slab8192_rk1_fp64.npz"))
+    N = int(gold["N"])
+    w0 = G.slab_state(N, int(gold["seed"]))
+    s0 = G.summarise(w0, N)
+    assert np.array_equal(s0["scattered"], gold["in_scattered"]) and s0["norm"] == float(gold["in_norm"])  # same input
+    w0 = torch.from_numpy(w0.astype(np.complex64)).cuda()
+    act = torch.from_numpy(gold["action"].astype(np.float32)).cuda()
+    for P in (1, 8):
+        sl = make_slab(N, float(gold["Re"]), torch.float32, P, dt=float(gold["dt"]))
+        sl.set_state(w0, act)
+        sl.rk_steps(1)
+        got = sl.get_state().cpu().numpy().astype(np.complex128)
+        sl.close()
+        s = G.summarise(got, N)
+        errs = dict(
+            norm=abs(s["norm"] / float(gold["out_norm"]) - 1),
+            low=rel_l2(s["low"], gold["out_low"]),
+            scattered=rel_l2(s["scattered"], gold["out_scattered"]),
+            nyq_row=rel_l2(s["scattered"][384:448], gold["out_scattered"][384:448]),
+            nyq_col=rel_l2(s["scattered"][448:], gold["out_scattered"][448:]),
+            row_bands=float(np.abs(s["row_bands"] / gold["out_row_bands"] - 1).max()),
+            col_bands=float(np.abs(s["col_bands"] / gold["out_col_bands"] - 1).max()),
+            nyq_col_norm=abs(s["nyq_col_norm"] / float(gold["out_nyq_col_norm"]) - 1),
+            # the step changed the state by 2.4 %: hold the CHANGE, not only the state, on the scattered entries
+            delta=rel_l2(s["scattered"] - gold["in_scattered"], gold["out_scattered"] - gold["in_scattered"]),
+            delta_low=rel_l2(s["low"] - gold["in_low"], gold["out_low"] - gold["in_low"]))
+        print(f"[slab 8192 vs oracle] P={P}: " + " ".join(f"{k}={v:.2e}" for k, v in errs.items()))
+        assert errs["norm"] < 1e-6 and errs["low"] < 2e-5 and errs["scattered"] < 2e-5, errs
+        assert errs["nyq_row"] < 5e-5 and errs["nyq_col"] < 5e-5, errs
+        assert errs["row_bands"] < 1e-5 and errs["col_bands"] < 1e-5 and errs["nyq_col_norm"] < 1e-5, errs
+        assert errs["delta"] < 1e-3 and errs["delta_low"] < 5e-3, errs

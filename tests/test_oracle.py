@@ -143,3 +143,22 @@ def test_energy_spectrum_sums_to_kinetic_energy():
     uh, vh = orc.compute_velocity_fft(one, env.kx, env.ky)
     assert abs(s1[5] - 2 * orc.compute_energy_mode(uh, vh, 3, 4, N, N)) < 1e-18
     assert s1.sum() == s1[5]
+
+
+def test_torch_cpu_port_matches_numpy_oracle():
+    """oracle/torch_cpu_port.py (the CPU baseline's torch / MKL variant) restates the same RK step."""
+    from oracle.torch_cpu_port import TorchCpuSolver
+    for dt_, tol in ((np.float64, 1e-13), (np.float32, 1e-6)):
+        for dealias in (False, True):
+            env = orc.KolmogorovFlow(dict(dt=1e-3), dict(Re=100, grid_size=(64, 64)), dtype=dt_, dealias=dealias)
+            rng = np.random.default_rng(0)
+            p = np.abs(np.fft.fftfreq(64, 1 / 64))[:, None]
+            q = np.arange(33)[None, :]
+            w0 = env.flow.initialize_state()[None] + (rng.normal(size=(3, 64, 33)) + 1j * rng.normal(size=(3, 64, 33))) \
+                * np.exp(-(p * p + q * q) / 64) * 64 * 64 * 0.1
+            w0 = w0.astype(orc._ctype(dt_))
+            acts = rng.uniform(-0.5, 0.5, (3, 4)).astype(dt_)
+            ch = env.equation.control_term(w0, env._control_field(acts, env.default_params))
+            a = env.integrator.rk_steps(w0.copy(), 5, ch)
+            b = TorchCpuSolver(env).rk_steps(w0, 5, ch)
+            assert np.linalg.norm(a - b) / np.linalg.norm(a) < tol
