@@ -58,6 +58,7 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=10, help="upper bound on the end-to-end steps (<= --steps)")
     ap.add_argument("--slab-grid", type=int, default=8192)
     ap.add_argument("--slab-steps", type=int, default=20)
+    ap.add_argument("--cpu-variant-job", default=None, help=argparse.SUPPRESS)  # internal: see cpu_variant
     return ap.parse_args()
 
 
@@ -144,35 +145,57 @@ def _cpu_worker_torch(job):
 def _run_jobs(jobs, nproc):
     import multiprocessing as mp
     t0 = time.perf_counter()
-    with mp.get_context("fork").Pool(nproc) as pool:  # always a child: the scipy variant patches the oracle module
+    with mp.get_context("fork").Pool(nproc) as pool:
         res = pool.map(_cpu_worker, jobs)
     return time.perf_counter() - t0, res
 
 
-def cpu_variant(args, rk_per_env_step, seconds, variant, ncores):
-    N = args.grid
+def _cpu_variant_here(a):
+    """Runs in a FRESH interpreter (see cpu_variant): no CUDA context, no thread pools inherited through fork."""
+    N, variant, ncores, seconds, dealias = a["grid"], a["variant"], a["ncores"], a["seconds"], a["dealias"]
     if variant == "numpy-procs":
-        _, res = _run_jobs([(N, args.re, args.dt, args.dtype, (0,), 2, args.dealias, 0)], 1)
+        res = [_cpu_worker((N, a["re"], a["dt"], a["dtype"], (0,), 2, dealias, 0))]
         per_rk = max(res[0][0] / 2, 1e-4)
         n_rk = int(max(4, min(5000, seconds / per_rk)))
-        jobs = [(N, args.re, args.dt, args.dtype, (i,), n_rk, args.dealias, 0) for i in range(ncores)]
-        wall, res = _run_jobs(jobs, ncores)
+        jobs = [(N, a["re"], a["dt"], a["dtype"], (i,), n_rk, dealias, 0) for i in range(ncores)]
+        _, res = _run_jobs(jobs, ncores)
         envs, what = ncores, f"{ncores} envs (one per process, np.fft single-threaded each)"
     else:
         torch_variant = variant == "torch-mkl"
         envs = 4 * ncores if torch_variant else ncores
         ids = tuple(range(envs))
         thr = -ncores if torch_variant else ncores
-        _, res = _run_jobs([(N, args.re, args.dt, args.dtype, ids, 2, args.dealias, thr)], 1)
+        res = [_cpu_worker((N, a["re"], a["dt"], a["dtype"], ids, 2, dealias, thr))]
         per_rk = max(res[0][0] / 2, 1e-4)
         n_rk = int(max(4, min(5000, seconds / per_rk)))
-        wall, res = _run_jobs([(N, args.re, args.dt, args.dtype, ids, n_rk, args.dealias, thr)], 1)
+        res = [_cpu_worker((N, a["re"], a["dt"], a["dtype"], ids, n_rk, dealias, thr))]
         what = (f"{envs} envs batched in one process, torch CPU tensors, {ncores} intra-op threads" if torch_variant
                 else f"{envs} envs batched in one process, scipy.fft workers={ncores}")
-    compute = max(r[0] for r in res)  # the timed rk_steps loop (pool start-up and state set-up excluded)
+    compute = max(r[0] for r in res)  # the timed rk_steps loop (process start-up and state set-up excluded)
     env_rk_per_s = envs * n_rk / compute
-    return dict(variant=variant, value=env_rk_per_s / rk_per_env_step, rk_steps_env_per_s=env_rk_per_s, threads=ncores,
-                sample=f"{what} x {n_rk} RK steps at {N}^2 {args.dtype}, {compute:.1f}s", finite=all(r[1] for r in res))
+    return dict(variant=variant, rk_steps_env_per_s=env_rk_per_s, threads=ncores,
+                sample=f"{what} x {n_rk} RK steps at {N}^2 {a['dtype']}, {compute:.1f}s", finite=all(r[1] for r in res))
+
+
+def cpu_variant(args, rk_per_env_step, seconds, variant, ncores):
+    """One CPU variant, timed in a fresh interpreter: the bench process holds a CUDA context and torch / OpenMP thread
+    pools, and a fork()ed child that touches a threaded library again can dead-lock."""
+    job = dict(grid=args.grid, re=args.re, dt=args.dt, dtype=args.dtype, dealias=bool(args.dealias), variant=variant,
+               ncores=ncores, seconds=seconds)
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    limit = 60.0 + 6.0 * seconds
+    try:
+        out = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-variant-job", json.dumps(job)],
+                             capture_output=True, text=True, timeout=limit, env=env, cwd=ROOT)
+        r = json.loads(out.stdout.strip().splitlines()[-1])
+    except subprocess.TimeoutExpired:
+        return dict(variant=variant, value=0.0, rk_steps_env_per_s=0.0, threads=ncores, finite=False,
+                    sample=f"timed out after {limit:.0f}s")
+    except Exception as e:
+        return dict(variant=variant, value=0.0, rk_steps_env_per_s=0.0, threads=ncores, finite=False,
+                    sample=f"failed: {type(e).__name__}: {e}")
+    r["value"] = r["rk_steps_env_per_s"] / rk_per_env_step
+    return r
 
 
 def cpu_baseline(args, rk_per_env_step, seconds, variants=("numpy-procs", "scipy-fft", "torch-mkl")):
@@ -501,8 +524,10 @@ def run_native(args):
     w_host = torch.from_numpy(initial_states(N, range(rank * B, (rank + 1) * B), npdt, literal)).pin_memory()
     w = w_host.to(dev)
     w_seed = w.clone() if literal else None
+    log(f"rank {rank}: headline warm-up ({args.warmup} env-steps)")
     timed_steps(st, w, w_seed, 0, args.warmup, True)
     barrier()
+    log(f"headline timed region ({args.steps} env-steps)")
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -511,6 +536,7 @@ def run_native(args):
     value = world * B * args.steps / t_dev
     step_gbs = 70.0 * C * B * rk * args.steps / t_dev / 1e9  # per GPU (t_dev is the max over ranks)
 
+    log(f"value = {value:.3f} env-steps/s, whole-step {step_gbs / peak:.3f} of peak, nonfinite {nonfinite}; e2e next")
     # ---- end-to-end through the C ABI with host buffers: `e2e` ------------------------------------------------
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     obs_h = torch.empty((B, st.obs_size ** 2), dtype=tdt).pin_memory()
@@ -531,6 +557,7 @@ def run_native(args):
     h2d = w_e2e.numel() * w_e2e.element_size() + B * 4 * wbytes
     d2h = w_e2e.numel() * w_e2e.element_size() + obs_h.numel() * wbytes + B * wbytes + B * 4
 
+    log(f"e2e = {e2e_value:.3f} env-steps/s; kernel profile next")
     # ---- roofline of the dominant kernel (column kernel), CUDA events inside the real launch sequence ---------
     ms_col, ms_row = st.profile_kernels(reps=40)
     chunk, lanes = st.chunk, st.lanes
@@ -550,6 +577,7 @@ def run_native(args):
     # ---- the same workload with the intended 2/3 mask ON, synthetic random fields (NOT the reference's arithmetic) --
     masked = None
     if literal and not args.no_extras and args.masked_steps > 0:
+        log("masked record")
         stm = KolmogorovStepper(grid_size=(N, N), Re=args.re, dt=args.dt, n_inner=n_inner, n_outer=n_outer, num_envs=B,
                                 dtype=tdt, device=dev, dealias=True, chunk=args.chunk)
         wm = torch.from_numpy(initial_states(N, range(rank * B, (rank + 1) * B), npdt, False)).to(dev)
@@ -582,10 +610,12 @@ def run_native(args):
     # ---- extra records: the other BASELINE.json configurations and the slab-decomposed single grid -------------
     extra = {}
     if not args.no_extras:
+        log("extra.configs")
         try:
             extra["configs"] = extra_configs(torch, dev, world, max_over_ranks, peak)
         except Exception as e:  # never lose the headline line to an extra record
             extra["configs_error"] = f"{type(e).__name__}: {e}"
+        log("extra.slab")
         try:
             extra["slab"] = slab_record(torch, dist, args, dev, rank, world, max_over_ranks, peak)
         except Exception as e:
@@ -627,6 +657,7 @@ def run_native(args):
         if extra:
             line["extra"] = extra
         if world == 1 and not args.no_cpu_baseline:
+            log("cpu_baseline")
             line["cpu_baseline"] = cpu_baseline(args, rk, args.cpu_seconds)
         print(json.dumps(_clean(line)), flush=True)
     if world > 1:
@@ -634,8 +665,16 @@ def run_native(args):
         dist.destroy_process_group()
 
 
+def log(msg):
+    """Progress on stderr (stdout carries the ONE JSON line)."""
+    print(f"[bench {time.strftime('%H:%M:%S')}] {msg}", file=sys.stderr, flush=True)
+
+
 def main():
     args = parse_args()
+    if args.cpu_variant_job:
+        print(json.dumps(_clean(_cpu_variant_here(json.loads(args.cpu_variant_job)))), flush=True)
+        return
     if args.impl == "reference":
         run_reference(args)
     else:

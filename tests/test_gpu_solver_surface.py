@@ -79,7 +79,7 @@ def test_dense_control_field_on_two_lanes_matches_oracle():
     """The dense spectrum is shared by both lanes of a large fp32 batch (graph replay included)."""
     from oracle import kolmogorov_oracle as orc
     from hydrogym_b200 import KolmogorovStepper
-    N, B, steps = 128, 64, 9
+    N, B, steps = 128, 128, 9
     ref = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=np.float32)
     rng = np.random.default_rng(3)
     p = np.abs(np.fft.fftfreq(N, 1.0 / N))[:, None]
