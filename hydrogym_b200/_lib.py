@@ -23,6 +23,7 @@ SYMBOLS = (
     "kf_slab_export", "kf_slab_exchange_bytes", "kf_slab_col", "kf_slab_row", "kf_slab_obs",
     "kf_slab_launch_count", "kf_slab_workspace_bytes", "kf_energy_spectrum",
     "kf_slab_p2p_init", "kf_slab_p2p_attach", "kf_slab_p2p_attach_local", "kf_physical_fields",
+    "kf_slab_barrier", "kf_slab_rk_steps",
     "kf_set_control_field", "kf_nonlinear_terms", "kf_linear_terms", "kf_implicit_timestep", "kf_strain_diagnostics",
 )
 
@@ -95,7 +96,10 @@ def load():
     lib.kf_slab_p2p_init.argtypes = [vp, vp]
     lib.kf_slab_p2p_attach.argtypes = [vp, vp]
     lib.kf_slab_p2p_attach_local.argtypes = [vp, ctypes.POINTER(vp)]
-    for name in ("kf_slab_p2p_init", "kf_slab_p2p_attach", "kf_slab_p2p_attach_local"):
+    lib.kf_slab_barrier.argtypes = [vp, vp]
+    lib.kf_slab_rk_steps.argtypes = [vp, ctypes.c_int, vp]
+    for name in ("kf_slab_p2p_init", "kf_slab_p2p_attach", "kf_slab_p2p_attach_local", "kf_slab_barrier",
+                 "kf_slab_rk_steps"):
         getattr(lib, name).restype = ctypes.c_int
     lib.kf_physical_fields.argtypes = [vp, vp, vp, ctypes.c_int, vp]
     lib.kf_physical_fields.restype = ctypes.c_int

@@ -289,6 +289,13 @@ int Impl<T, P, TC, GROUPS, CB, RB, TB>::tma_setup(Ctx& c) {
 #define KF_F256_TB 2
 #endif
 #define KF_CFG_F256 KF_F256_TC, KF_F256_GROUPS, KF_F256_CB, KF_F256_RB, KF_F256_TB
+#ifndef KF_F256_TPF  // FFT plan of the 256^2 fp32 kernels: threads per transform and the radix sequence
+#define KF_F256_TPF 16
+#define KF_F256_R0 16
+#define KF_F256_R1 16
+#define KF_F256_R2 1
+#endif
+#define KF_PLAN_F256 256, KF_F256_TPF, KF_F256_R0, KF_F256_R1, KF_F256_R2
 // fp64: 16 elements per thread (one exchange fewer per transform than 8) beats the lower register pressure of 8:
 // 256^2 row kernel 242 -> 186 us, column kernel 300 -> 278 us per launch (256 envs)
 #ifndef KF_D256_RB
@@ -342,7 +349,7 @@ const Ops* find_ops(int dtype, int N) {
   using kf::Plan;
   static const Ops f64_[] = {Impl<float, Plan<64, 8, 8, 8>, 16, 16>::make()};
   static const Ops f128[] = {Impl<float, Plan<128, 8, 16, 8>, KF_CFG_F128>::make()};
-  static const Ops f256[] = {Impl<float, Plan<256, 16, 16, 16>, KF_CFG_F256>::make()};
+  static const Ops f256[] = {Impl<float, Plan<KF_PLAN_F256>, KF_CFG_F256>::make()};
   static const Ops f512[] = {Impl<float, Plan<512, 32, 8, 8, 8>, 8, 4>::make()};
   static const Ops f1024[] = {Impl<float, Plan<KF_PLAN_F1024>, KF_CFG_F1024>::make()};
   static const Ops d64[] = {Impl<double, Plan<64, 8, 8, 8>, 16, 16>::make()};

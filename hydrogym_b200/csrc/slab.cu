@@ -65,7 +65,45 @@ struct SlabCtx {
   // the one-CTA kernel of the packed column runs beside the main column kernel on its own stream
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // device-side cross-rank barrier (peer-to-peer mode, one process per GPU): flag words behind own_adv
+  // ([0..P) = arrival epochs written by the peers, [KF_MAX_PEERS] = this rank's epoch counter)
+  unsigned* flags = nullptr;
+  unsigned* peer_flags[KF_MAX_PEERS] = {};
+  bool local_peers = false;  // emulated ranks in one process: stream order is the barrier
+  // one RK solver step (5 sub-stages) as a CUDA graph, replayed by kf_slab_rk_steps
+  cudaGraphExec_t graph = nullptr;
 };
+
+// Cross-rank barrier as ONE small kernel per rank (replaces a 1-element NCCL all-reduce and can be captured in a CUDA
+// graph): every rank bumps its epoch, writes it into slot `rank` of every peer's flag block over NVLink
+// (st.release.sys) and spins until all P slots of its own block have reached the epoch (ld.acquire.sys).  The stream
+// orders it after the kernels whose peer stores it publishes, and before the kernels that read what the peers stored.
+// Ranks live on DIFFERENT GPUs (never launched for emulated ranks sharing a device), so every spinning kernel is
+// resident while it waits.
+struct BarrierArgs {
+  unsigned* mine;
+  unsigned* peers[KF_MAX_PEERS];
+  int rank, P;
+};
+
+__global__ void slab_barrier_kernel(BarrierArgs a) {
+  __shared__ unsigned s_epoch;
+  if (threadIdx.x == 0) s_epoch = ++a.mine[KF_MAX_PEERS];
+  __syncthreads();
+  const unsigned e = s_epoch;
+  __threadfence_system();
+  if ((int)threadIdx.x < a.P) {
+    unsigned* dst = a.peers[threadIdx.x] + a.rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(e) : "memory");
+    const unsigned* src = a.mine + threadIdx.x;
+    unsigned v;
+    do {
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(src) : "memory");
+      if ((int)(v - e) < 0) __nanosleep(64);
+    } while ((int)(v - e) < 0);
+  }
+  __syncthreads();
+}
 
 template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS, int CMINB = 2, int TWS = 0> struct SlabImpl {
   static_assert(PH::L * 2 == P::L, "the row kernel's plan is half the grid size");
@@ -256,6 +294,7 @@ void free_all(SlabCtx& c) {
       cudaIpcCloseMemHandle(c.peer_adv[d]);
     }
   }
+  if (c.graph) cudaGraphExecDestroy(c.graph);
   if (c.side) cudaStreamDestroy(c.side);
   if (c.ev_fork) cudaEventDestroy(c.ev_fork);
   if (c.ev_join) cudaEventDestroy(c.ev_join);
@@ -482,7 +521,8 @@ int kf_slab_p2p_init(kf_slab h, void* ipc_handles_out) {
   const size_t tile = c.ops->elem * (size_t)c.N * c.Q;
   if (!c.own_fld) {
     if (int rc = dev_alloc(c, &c.own_fld, 4 * tile)) return rc;
-    if (int rc = dev_alloc(c, &c.own_adv, tile)) return rc;
+    if (int rc = dev_alloc(c, &c.own_adv, tile + 4096)) return rc;  // + the barrier's flag block (zeroed)
+    c.flags = (unsigned*)((char*)c.own_adv + tile);
   }
   if (ipc_handles_out) {
     cudaIpcMemHandle_t* out = (cudaIpcMemHandle_t*)ipc_handles_out;
@@ -508,7 +548,10 @@ int kf_slab_p2p_attach(kf_slab h, const void* all_handles) {
     KF_CUDA(cudaIpcOpenMemHandle(&c.peer_adv[d], hs[2 * d + 1], cudaIpcMemLazyEnablePeerAccess));
     c.ipc_opened[d] = true;
   }
+  const size_t tile = c.ops->elem * (size_t)c.N * c.Q;
+  for (int d = 0; d < c.P; ++d) c.peer_flags[d] = (unsigned*)((char*)c.peer_adv[d] + tile);
   c.p2p = true;
+  c.local_peers = false;
   return 0;
 }
 
@@ -521,6 +564,84 @@ int kf_slab_p2p_attach_local(kf_slab h, const kf_slab* peers) {
     c.peer_adv[d] = peers[d]->c.own_adv;
   }
   c.p2p = true;
+  c.local_peers = true;
+  return 0;
+}
+
+namespace {
+
+void enqueue_barrier(SlabCtx& c, cudaStream_t s) {
+  if (c.P == 1 || c.local_peers) return;  // one rank, or emulated ranks on one stream: stream order suffices
+  BarrierArgs a;
+  a.mine = c.flags;
+  for (int d = 0; d < KF_MAX_PEERS; ++d) a.peers[d] = d < c.P ? c.peer_flags[d] : nullptr;
+  a.rank = c.rank;
+  a.P = c.P;
+  slab_barrier_kernel<<<1, 32, 0, s>>>(a);
+  c.launches += 1;
+}
+
+// one RK solver step in peer-to-peer mode: 5 x (row kernel, barrier, column pass, barrier)
+void enqueue_rk_step(SlabCtx& c, cudaStream_t s) {
+  for (int stage = 0; stage < 5; ++stage) {
+    c.ops->row(c, nullptr, nullptr, s);
+    enqueue_barrier(c, s);  // every rank's advection blocks have landed
+    c.ops->col(c, stage, nullptr, nullptr, s);
+    enqueue_barrier(c, s);  // every rank's field blocks have landed
+    c.launches += 4 + (c.rank == 0 ? 1 : 0);
+  }
+}
+
+}  // namespace
+
+int kf_slab_barrier(kf_slab h, void* stream) {
+  if (!h) return fail("kf_slab_barrier: null handle");
+  SlabCtx& c = h->c;
+  if (!c.p2p) return fail("kf_slab_barrier: peer-to-peer exchange not attached");
+  DeviceGuard guard(c.cfg.device);
+  enqueue_barrier(c, (cudaStream_t)stream);
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int kf_slab_rk_steps(kf_slab h, int n_steps, void* stream) {
+  if (!h) return fail("kf_slab_rk_steps: null handle");
+  if (n_steps < 0) return fail("kf_slab_rk_steps: n_steps must be >= 0");
+  SlabCtx& c = h->c;
+  if (!c.p2p) return fail("kf_slab_rk_steps: needs the peer-to-peer exchange (kf_slab_p2p_init / attach)");
+  if (c.local_peers && c.P > 1)
+    return fail("kf_slab_rk_steps: emulated ranks in one process must be interleaved by the host (kf_slab_row / kf_slab_col)");
+  if (!c.have_constants) return fail("kf_slab_set_constants has not been called");
+  DeviceGuard guard(c.cfg.device);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!c.graph && n_steps >= 2) {
+    // capture on a private stream (the caller's may be the legacy default stream, which cannot capture)
+    cudaStream_t cs = nullptr;
+    KF_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    cudaGraph_t g = nullptr;
+    const long long before = c.launches;
+    cudaError_t ce = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+    if (ce == cudaSuccess) {
+      enqueue_rk_step(c, cs);
+      ce = cudaStreamEndCapture(cs, &g);
+    }
+    c.launches = before;
+    cudaStreamDestroy(cs);
+    if (ce != cudaSuccess) return fail(std::string("kf_slab_rk_steps: graph capture: ") + cudaGetErrorString(ce));
+    ce = cudaGraphInstantiate(&c.graph, g, 0);
+    cudaGraphDestroy(g);
+    if (ce != cudaSuccess) return fail(std::string("kf_slab_rk_steps: cudaGraphInstantiate: ") + cudaGetErrorString(ce));
+  }
+  const long long per_step = 5LL * (4 + (c.rank == 0 ? 1 : 0) + (c.P > 1 ? 2 : 0));
+  for (int i = 0; i < n_steps; ++i) {
+    if (c.graph) {
+      KF_CUDA(cudaGraphLaunch(c.graph, s));
+      c.launches += per_step;
+    } else {
+      enqueue_rk_step(c, s);
+    }
+  }
+  KF_CUDA(cudaGetLastError());
   return 0;
 }
 

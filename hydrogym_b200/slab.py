@@ -68,7 +68,8 @@ class SlabKolmogorovSolver:
 
     def __init__(self, grid_size=(8192, 8192), Re=1000, k=4, control_ks=(4, 5, 6, 7), dt=1e-3,
                  dtype=torch.float32, device=None, dealias=False, obs_size=8, min_action=-0.5, max_action=0.5,
-                 domain_y=(0, 2 * np.pi), group=None, local_ranks=None, zero_forcing=False, exchange="nccl"):
+                 domain_y=(0, 2 * np.pi), group=None, local_ranks=None, zero_forcing=False, exchange="nccl",
+                 use_graph=True, device_barrier=True):
         if exchange not in ("nccl", "p2p"):
             raise ValueError("exchange must be 'nccl' (all_to_all_single) or 'p2p' (stores into peer-mapped buffers)")
         if dtype not in (torch.float32, torch.float64):
@@ -97,6 +98,7 @@ class SlabKolmogorovSolver:
             else:
                 self.world, my_ranks = 1, [0]
         self.p2p = exchange == "p2p"
+        self.use_graph, self.device_barrier = bool(use_graph), bool(device_barrier)
         self._flag = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._lib = _lib.load()
         cfg = _lib.KfConfig(N=N, M=M, B=1, dtype=_lib.KF_F32 if dtype == torch.float32 else _lib.KF_F64,
@@ -156,8 +158,13 @@ class SlabKolmogorovSolver:
 
     def _rank_barrier(self):
         """Stream-ordered cross-rank barrier: every rank's earlier kernels (and their peer stores) are complete
-        before any rank's later kernels start."""
-        if not self.local and self.world > 1:
+        before any rank's later kernels start.  Peer-to-peer mode: one small kernel per rank on epoch flags in the
+        peer-mapped buffers (``kf_slab_barrier``); otherwise a 1-element NCCL all-reduce."""
+        if self.local or self.world == 1:
+            return
+        if self.p2p and self.device_barrier:
+            _lib.check(self._lib.kf_slab_barrier(self._ranks[0].h, self._stream()), "kf_slab_barrier")
+        else:
             dist.all_reduce(self._flag, group=self.group)
 
     def _all_to_all(self, which):
@@ -228,9 +235,15 @@ class SlabKolmogorovSolver:
                 _lib.check(self._lib.kf_slab_set_action(r.h, _ptr(action), self._stream()), "kf_slab_set_action")
 
     def rk_steps(self, n_steps):
-        """Advance the loaded state by ``n_steps`` RK solver steps (5 sub-stages, 10 all-to-alls each)."""
+        """Advance the loaded state by ``n_steps`` RK solver steps (5 sub-stages, 10 all-to-alls each).  In
+        peer-to-peer mode with one rank per process the whole step is ONE CUDA graph per rank replayed by
+        ``kf_slab_rk_steps`` (device-side barriers, no host call per sub-stage)."""
         with torch.cuda.device(self.device):
             s = self._stream()
+            if self.p2p and self.use_graph and not (self.local and self.world > 1):
+                _lib.check(self._lib.kf_slab_rk_steps(self._ranks[0].h, int(n_steps), s), "kf_slab_rk_steps")
+                self.rk_steps_done += int(n_steps)
+                return
             for _ in range(int(n_steps)):
                 for stage in range(5):
                     for r in self._ranks:

@@ -184,6 +184,14 @@ int kf_slab_obs(kf_slab h, const void* fld_recv_dev, double* acc4_dev, void* obs
 int kf_slab_p2p_init(kf_slab h, void* ipc_handles_out);
 int kf_slab_p2p_attach(kf_slab h, const void* all_handles);
 int kf_slab_p2p_attach_local(kf_slab h, const kf_slab* peers);
+/* Peer-to-peer mode, one process per GPU.  kf_slab_barrier: the cross-rank barrier as one small kernel on `stream`
+ * (epoch flags in the peer-mapped buffers, st.release.sys / ld.acquire.sys) -- no NCCL call, capturable.
+ * kf_slab_rk_steps: n_steps RK solver steps, each 5 x (row kernel, barrier, column pass, barrier), replayed from ONE
+ * CUDA graph per rank (the whole of RK4_CN.time_step_fn, hydrogym/jax/solvers/base.py:50-57, without a host call per
+ * sub-stage).  Expects the x-space fields of the current state in the receive buffers (kf_slab_col(stage < 0) +
+ * kf_slab_barrier) and leaves them there.  Not for emulated ranks sharing one device (the host interleaves those). */
+int kf_slab_barrier(kf_slab h, void* stream);
+int kf_slab_rk_steps(kf_slab h, int n_steps, void* stream);
 long long kf_slab_launch_count(kf_slab h);
 size_t kf_slab_workspace_bytes(kf_slab h);
 

@@ -34,8 +34,12 @@ def _worker(rank, world, port, N, steps, exchange, out):
     try:
         w0 = torch.from_numpy(_state(N, 9)).cuda()
         act = torch.tensor([0.2, -0.4, 0.1, 0.3], device="cuda")
-        sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device=f"cuda:{rank}",
-                                  exchange=exchange)
+        # "p2p": ONE CUDA graph per RK step with device-side flag barriers (kf_slab_rk_steps);
+        # "p2p-hostloop": the same kernels issued sub-stage by sub-stage from the host, device-side barriers;
+        # "p2p-ncclbarrier": host loop with the 1-element NCCL all-reduce as the barrier
+        kw = dict(exchange="p2p", use_graph=exchange == "p2p", device_barrier=exchange != "p2p-ncclbarrier") \
+            if exchange.startswith("p2p") else dict(exchange="nccl")
+        sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device=f"cuda:{rank}", **kw)
         assert sl.world == world
         sl.set_state(w0, act)
         sl.rk_steps(steps)
@@ -48,7 +52,7 @@ def _worker(rank, world, port, N, steps, exchange, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("exchange", ["nccl", "p2p"])
+@pytest.mark.parametrize("exchange", ["nccl", "p2p", "p2p-hostloop", "p2p-ncclbarrier"])
 @pytest.mark.parametrize("N", [1024])
 def test_slab_nccl_matches_single_rank(N, exchange):
     world = torch.cuda.device_count()
@@ -57,7 +61,7 @@ def test_slab_nccl_matches_single_rank(N, exchange):
     world = 2 if world < 4 else (4 if world < 8 else 8)
     import torch.multiprocessing as mp
     from hydrogym_b200.slab import SlabKolmogorovSolver
-    steps = 2
+    steps = 3
     sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device="cuda:0", local_ranks=1)
     sl.set_state(torch.from_numpy(_state(N, 9)).cuda(), torch.tensor([0.2, -0.4, 0.1, 0.3], device="cuda"))
     sl.rk_steps(steps)
