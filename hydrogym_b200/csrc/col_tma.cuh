@@ -50,6 +50,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
 }
 // 2-D tiled TMA load: box at element coordinates (c0 = inner, c1 = row) -> dense [rows][inner] in smem
+__device__ __forceinline__ void tma_load_2d_hint(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
+                                                 uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], "
+      "[%4], %5;" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
@@ -58,14 +66,16 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       : "memory");
 }
 
-template <typename T, class P, int TC> struct ColTmaSmem {
+// XBUF: a dedicated exchange buffer of N x TC lane-paired complex numbers for the inverse transforms (one exchange
+// round, two barriers) instead of reusing the h tile for a split exchange (two rounds, four barriers).
+template <typename T, class P, int TC, bool XBUF = false> struct ColTmaSmem {
   static constexpr int N = P::L;
   static constexpr size_t kTile = (size_t)N * TC * sizeof(Cx<T>);
   static_assert(kTile == col_exchange_bytes<T, N, TC>(), "a tile buffer doubles as the exchange buffer");
-  static constexpr size_t bytes() { return 3 * kTile + 2 * (size_t)N * sizeof(Cx<T>) + 64; }
+  static constexpr size_t bytes() { return (XBUF ? 5 : 3) * kTile + 2 * (size_t)N * sizeof(Cx<T>) + 64; }
 };
 
-template <typename T, class P, int TC, int MINB>
+template <typename T, class P, int TC, int MINB, bool XBUF = false>
 __global__ void __launch_bounds__(P::TPF* TC, MINB)
     col_tma_kernel(StageArgs<T> a, const __grid_constant__ CUtensorMap m_adv, const __grid_constant__ CUtensorMap m_h,
                    const __grid_constant__ CUtensorMap m_w, int ntiles) {
@@ -77,7 +87,8 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
   Cx<T>* buf_adv = reinterpret_cast<Cx<T>*>(smem_tma);
   Cx<T>* buf_h = buf_adv + kTileEl;
   Cx<T>* buf_w = buf_h + kTileEl;
-  Cx<T>* s_tw = buf_w + kTileEl;
+  Cx<T>* s_xbuf = buf_w + kTileEl;  // 2 tiles, only with XBUF
+  Cx<T>* s_tw = s_xbuf + (XBUF ? 2 * kTileEl : 0);
   Cx<T>* s_nyq = s_tw + N;
   uint64_t* bar = reinterpret_cast<uint64_t*>(s_nyq + N);  // [3]: adv, h, w
   const int tid = threadIdx.x, c = tid % TC, t = tid / TC;
@@ -101,13 +112,17 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     if (pos < nb) { b = pos; tx = 0; }
     else { constexpr int TM1 = TILES > 1 ? TILES - 1 : 1; const int r = pos - nb; b = r / TM1; tx = 1 + (r - b * TM1); }
   };
+  const uint64_t pol_state = l2_policy(a.l2_hints != 0);  // omega_hat / h: streamed when the hints are on
   auto issue = [&](Cx<T>* buf, const CUtensorMap* map, uint64_t* br, int tile) {
     int b, tx;
     decode(tile, b, tx);
     mbar_expect_tx(br, kBytes);
+    const bool state = (map != &m_adv);
 #pragma unroll
-    for (int r = 0; r < NBOX; ++r)
-      tma_load_2d(buf + (size_t)r * RB * TC, map, tx * TC * 2, b * N + r * RB, br);
+    for (int r = 0; r < NBOX; ++r) {
+      if (state) tma_load_2d_hint(buf + (size_t)r * RB * TC, map, tx * TC * 2, b * N + r * RB, br, pol_state);
+      else tma_load_2d(buf + (size_t)r * RB * TC, map, tx * TC * 2, b * N + r * RB, br);
+    }
   };
   constexpr int km = ((MH + 1) * 2) / 3;  // 2/3 mask: columns ky >= km of the advection term are discarded
 
@@ -184,9 +199,9 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
       Cx<T>* wmain = a.wmain + b * plane + q;
       Cx<T>* hmain = a.hmain + b * plane + q;
       rk_update_column<T, P>(a, v, w, g0, use_h, t, q,
-                             [&](int, int kx, Cx<T> h) { if (a.store_h) stc(hmain + (size_t)kx * MH, h); },
+                             [&](int, int kx, Cx<T> h) { if (a.store_h) stc_hint(hmain + (size_t)kx * MH, h, pol_state); },
                              [&](int, int kx, Cx<T> wn) {
-                               stc(wmain + (size_t)kx * MH, wn);
+                               stc_hint(wmain + (size_t)kx * MH, wn, pol_state);
                                stc(buf_w + kx * TC + c, wn);
                              },
                              [&](int, int kx) { return ldc(buf_h + kx * TC + c); },
@@ -198,12 +213,23 @@ __global__ void __launch_bounds__(P::TPF* TC, MINB)
     }
 
     auto load_w = [&](int, int kx) { return ldc(buf_w + kx * TC + c); };
-    col_field_pair<0, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
-    col_field_pair<1, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
+    if constexpr (XBUF) {
+      // buf_h is free as soon as the RK update is done (the barrier above): re-arm it a whole inverse-transform
+      // phase earlier than the omega_hat tile
+      if (tid == 0 && has_next && use_h) {
+        fence_proxy_async();
+        issue(buf_h, &m_h, bar + 1, next);
+      }
+      col_field_pair<0, T, P, TC, false>(a, load_w, s_tw, s_nyq, s_xbuf, c, t, q, b, special);
+      col_field_pair<1, T, P, TC, false>(a, load_w, s_tw, s_nyq, s_xbuf, c, t, q, b, special);
+    } else {
+      col_field_pair<0, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
+      col_field_pair<1, T, P, TC>(a, load_w, s_tw, s_nyq, buf_h, c, t, q, b, special);
+    }
     __syncthreads();  // every thread has read its omega_hat for the second pair and left the last exchange
     if (tid == 0 && has_next) {
       fence_proxy_async();
-      if (use_h) issue(buf_h, &m_h, bar + 1, next);
+      if (use_h && !XBUF) issue(buf_h, &m_h, bar + 1, next);
       issue(buf_w, &m_w, bar + 2, next);
     }
   }

@@ -22,6 +22,8 @@
 //             instruction (F2 lanes: FFMA2 / FADD2 / FMUL2) with 128-bit accesses.
 // Wavenumbers are the integers p = fftfreq index, q = rfftfreq index (2*pi*kx = p).
 #pragma once
+#include <cstdint>
+
 #include "fft.cuh"
 
 namespace kf {
@@ -43,7 +45,25 @@ template <typename T> struct StageArgs {
   T scale;             // 1/(N*M), folded into the prologue
   int dealias;
   int store_h;         // 0 in the last sub-stage: the next RK step starts with beta = 0 and never reads h
+  int l2_hints;        // 1: omega_hat / h tiles are loaded and stored with the L2 evict_first policy (they are touched
+                       // once per sub-stage and only by the column kernel) so that the x-space fields and the
+                       // advection rows -- produced by one kernel and consumed by the next -- keep the L2
 };
+
+// L2 cache policies (createpolicy): evict_first for streamed data, evict_normal otherwise
+__device__ __forceinline__ uint64_t l2_policy(bool evict_first) {
+  uint64_t p;
+  if (evict_first) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+// 64-bit / 128-bit global stores with an L2 policy
+__device__ __forceinline__ void stc_hint(Cx<float>* p, Cx<float> a, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.v2.f32 [%0], {%1, %2}, %3;" ::"l"(p), "f"(a.x), "f"(a.y), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void stc_hint(Cx<double>* p, Cx<double> a, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.v2.f64 [%0], {%1, %2}, %3;" ::"l"(p), "d"(a.x), "d"(a.y), "l"(pol) : "memory");
+}
 
 // exchange policy of the column kernel: TC columns interleaved, conflict-free
 template <typename X, int TC> struct ColEx {
@@ -151,7 +171,9 @@ template <typename T, int N, int TC> __host__ __device__ constexpr size_t col_ex
 // spectral fields of omega_hat (w[] in registers), inverse x-FFT, store to FA/FB.
 // Thread (c, t) owns column q = tile*TC + c and rows {t + TPF*m}.
 // ---------------------------------------------------------------------------
-template <int PAIR, typename T, class P, int TC, class LoadW>
+// SPLIT: the exchange buffer holds N x TC lane values (real and imaginary parts go through it in two rounds, four
+// barriers per exchange); !SPLIT: it holds N x TC lane-paired complex numbers (one round, two barriers).
+template <int PAIR, typename T, class P, int TC, bool SPLIT = true, class LoadW>
 __device__ __forceinline__ void col_field_pair(const StageArgs<T>& a, LoadW load_w, const Cx<T>* s_tw,
                                                const Cx<T>* s_nyq, void* s_exchange, int c, int t, int q, int b,
                                                bool special) {
@@ -187,8 +209,13 @@ __device__ __forceinline__ void col_field_pair(const StageArgs<T>& a, LoadW load
     }
     __syncthreads();
   }
-  ColExSplit<L2, TC> ex{reinterpret_cast<L2*>(s_exchange), c};
-  fft_regs<P, +1, L2>(v, s_tw, t, ex);
+  if constexpr (SPLIT) {
+    ColExSplit<L2, TC> ex{reinterpret_cast<L2*>(s_exchange), c};
+    fft_regs<P, +1, L2>(v, s_tw, t, ex);
+  } else {
+    ColEx<L2, TC> ex{reinterpret_cast<Cx<L2>*>(s_exchange), c};
+    fft_regs<P, +1, L2>(v, s_tw, t, ex);
+  }
   Cx<L2>* out = (PAIR == 0 ? a.fa : a.fb) + (size_t)b * N * MH + q;
 #pragma unroll
   for (int m = 0; m < E; ++m) stc(out + (size_t)(t + TPF * m) * MH, v[m]);
@@ -407,6 +434,19 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) row_kernel(StageArgs<T> 
   for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
   __syncthreads();
   pdl_wait();  // the fields below are the column kernel's output; the advection rows we write are its input
+
+  if (a.l2_hints & 2) {
+    // experiment: pull the SECOND row of every group into L1 now, so that its loads (issued after the first row's
+    // transform) see L1 latency; 2 * GROUPS rows x 2 arrays of MH lane-paired complex numbers, 128-byte lines
+    constexpr int kLinesPerRow = (int)(MH * sizeof(Cx<L2>) / 128);
+    for (int i = threadIdx.x; i < GROUPS * 2 * kLinesPerRow; i += TPF * GROUPS) {
+      const int gg = i / (2 * kLinesPerRow), rest = i - gg * 2 * kLinesPerRow;
+      const int arr = rest / kLinesPerRow, line = rest - arr * kLinesPerRow;
+      const size_t off = b * plane + (size_t)(2 * (blockIdx.x * GROUPS + gg) + 1) * MH;
+      const char* src = reinterpret_cast<const char*>((arr ? a.fb : a.fa) + off) + (size_t)line * 128;
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(src));
+    }
+  }
 
   Cx<T> v[E];
 #pragma unroll

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "col_tma.cuh"
+#include "resident.cuh"
 
 namespace {
 
@@ -67,6 +68,11 @@ struct Ops {
   void (*export_)(const struct Ctx&, int nb, void* user, size_t user_env, cudaStream_t);
   void (*export_h)(const struct Ctx&, int nb, void* user, size_t user_env, cudaStream_t);  // the RK register h
   void (*forcing)(const struct Ctx&, int nb, const void* actions, cudaStream_t);
+  void (*forcing_to)(const struct Ctx&, void* G, int nb, const void* actions, cudaStream_t);
+  // on-chip-resident RK steps (resident.cuh): whole batch, user layout in place; nullptr where the grid does not fit
+  cudaError_t (*resident_prepare)() = nullptr;
+  cudaError_t (*resident)(const struct Ctx&, void* omega_user, const void* G, int B, int n_steps, cudaStream_t) = nullptr;
+  int resident_cluster = 0;
 };
 
 struct Ctx {
@@ -90,15 +96,22 @@ struct Ctx {
   // dense control spectrum (general control_field of RungeKuttaCrankNicolson.solve): [N][MH] + [N]; owner = lane 0
   void *ctrl_main = nullptr, *ctrl_nyq = nullptr;
   bool ctrl_on = false, ctrl_owner = false;
+  // on-chip-resident path (small grids): forcing rows of the WHOLE batch
+  bool resident_on = false;
+  void* Gfull = nullptr;
   // TMA column kernel: tensor maps over advx / hmain / wmain and the persistent grid size
   CUtensorMap tm_adv, tm_h, tm_w;
   bool use_tma = false;
   int tma_ctas = 0;
   // programmatic dependent launch of the stage kernels (KF_PDL=1; see pdl_wait in kernels.cuh)
   bool pdl = false;
-  // CUDA graph of `graph_steps` RK steps on a full chunk
-  cudaGraphExec_t graph = nullptr;
-  int graph_steps = 0;
+  // CUDA graphs of 4 RK steps, one per number of environments they were captured for (a full chunk, and the
+  // balanced remainder of a batch that is not a multiple of lanes x chunk)
+  static constexpr int kGraphs = 2;
+  cudaGraphExec_t graph[kGraphs] = {nullptr, nullptr};
+  int graph_nb[kGraphs] = {0, 0};
+  // L2 policy hints (KF_L2_HINTS, default on when the chunk leaves the batch's persistent state no room in L2)
+  int l2_hints = 0;
   // Second lane: an identical chunk-sized workspace driven on its own stream.  Consecutive chunks alternate
   // between the lanes, so the row kernel of one chunk overlaps the column kernel of the other (they saturate
   // different parts of the machine): measured 0.956 -> 0.882 ms per RK step at 256^2 x 256 fp32.
@@ -110,7 +123,7 @@ struct Ctx {
 
 // TC: columns per column-kernel CTA; GROUPS: FFT groups per row-kernel CTA;
 // CB / RB: __launch_bounds__ min-blocks (register caps) of the column / row kernels.
-template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int TB = 1> struct Impl {
+template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int TB = 1, bool XB = false> struct Impl {
   using C = kf::Cx<T>;
   static constexpr int N = P::L, MH = N / 2;
   using C2 = kf::Cx<typename kf::PairOf<T>::type>;  // lane-paired complex (two transforms per element)
@@ -146,6 +159,7 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     a.scale = (T)(1.0 / ((double)N * (double)N));
     a.dealias = c.cfg.dealias;
     a.store_h = 1;
+    a.l2_hints = c.l2_hints;
     return a;
   }
 
@@ -204,13 +218,17 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     kf::forcing_row_kernel<T><<<dim3((MH + 1 + 127) / 128, nb), 128, 0, s>>>(
         (C*)c.G, (const C*)c.F, (const C*)c.C, (const T*)actions, (T)c.cfg.min_action, (T)c.cfg.max_action, MH + 1);
   }
+  static void forcing_to(const Ctx& c, void* G, int nb, const void* actions, cudaStream_t s) {
+    kf::forcing_row_kernel<T><<<dim3((MH + 1 + 127) / 128, nb), 128, 0, s>>>(
+        (C*)G, (const C*)c.F, (const C*)c.C, (const T*)actions, (T)c.cfg.min_action, (T)c.cfg.max_action, MH + 1);
+  }
   static int tma_setup(Ctx& c);
   static void col_tma(const Ctx& c, int nb, const Stage& st, cudaStream_t s) {
     kf::StageArgs<T> a = args(c);
     a.beta = (T)st.beta; a.gdt = (T)st.gdt; a.munu = (T)st.munu; a.store_h = st.store_h;
     const int ntiles = nb * (MH / TC);
     const int grid = ntiles < c.tma_ctas ? ntiles : c.tma_ctas;
-    launch_stage(c, kf::col_tma_kernel<T, P, TC, TB>, dim3(grid), P::TPF * TC, kf::ColTmaSmem<T, P, TC>::bytes(),
+    launch_stage(c, kf::col_tma_kernel<T, P, TC, TB, XB>, dim3(grid), P::TPF * TC, kf::ColTmaSmem<T, P, TC, XB>::bytes(),
                  s, a, c.tm_adv, c.tm_h, c.tm_w, ntiles);
   }
   static Ops make() {
@@ -219,7 +237,7 @@ template <typename T, class P, int TC, int GROUPS, int CB = 1, int RB = 1, int T
     o.tc = TC; o.col_threads = P::TPF * TC; o.row_groups = GROUPS; o.row_threads = P::TPF * GROUPS;
     o.col_smem = col_smem(); o.row_smem = row_smem();
     o.prepare = prepare; o.fill_tw = kf::fill_twiddles<P>; o.tma_setup = tma_setup; o.col_tma = col_tma; o.col = col; o.row = row; o.obs = obs; o.fields = fields; o.finalize = finalize;
-    o.import_ = import_; o.export_ = export_; o.export_h = export_h; o.forcing = forcing;
+    o.import_ = import_; o.export_ = export_; o.export_h = export_h; o.forcing = forcing; o.forcing_to = forcing_to;
     return o;
   }
 };
@@ -242,17 +260,19 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-template <typename T, class P, int TC, int GROUPS, int CB, int RB, int TB>
-int Impl<T, P, TC, GROUPS, CB, RB, TB>::tma_setup(Ctx& c) {
+template <typename T, class P, int TC, int GROUPS, int CB, int RB, int TB, bool XB>
+int Impl<T, P, TC, GROUPS, CB, RB, TB, XB>::tma_setup(Ctx& c) {
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) return fail("cuTensorMapEncodeTiled is not available from this driver");
-  const size_t smem = kf::ColTmaSmem<T, P, TC>::bytes();
-  auto kern = kf::col_tma_kernel<T, P, TC, TB>;
+  const size_t smem = kf::ColTmaSmem<T, P, TC, XB>::bytes();
+  auto kern = kf::col_tma_kernel<T, P, TC, TB, XB>;
   KF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0, sms = 0;
   KF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, P::TPF * TC, smem));
   KF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c.cfg.device));
   if (per_sm < 1) return fail("col_tma_kernel does not fit on an SM");
+  if (const char* e = std::getenv("KF_COL_PER_SM"))  // experiment: fewer resident column CTAs leave room for row CTAs
+    if (std::atoi(e) >= 1 && std::atoi(e) < per_sm) per_sm = std::atoi(e);
   c.tma_ctas = per_sm * sms;
   const CUtensorMapDataType dt = sizeof(T) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64;
   const cuuint64_t dims[2] = {(cuuint64_t)(2 * MH), (cuuint64_t)c.chunk * N};
@@ -288,7 +308,10 @@ int Impl<T, P, TC, GROUPS, CB, RB, TB>::tma_setup(Ctx& c) {
 #ifndef KF_F256_TB
 #define KF_F256_TB 2
 #endif
-#define KF_CFG_F256 KF_F256_TC, KF_F256_GROUPS, KF_F256_CB, KF_F256_RB, KF_F256_TB
+#ifndef KF_F256_XB
+#define KF_F256_XB false
+#endif
+#define KF_CFG_F256 KF_F256_TC, KF_F256_GROUPS, KF_F256_CB, KF_F256_RB, KF_F256_TB, KF_F256_XB
 #ifndef KF_F256_TPF  // FFT plan of the 256^2 fp32 kernels: threads per transform and the radix sequence
 #define KF_F256_TPF 16
 #define KF_F256_R0 16
@@ -345,14 +368,59 @@ int Impl<T, P, TC, GROUPS, CB, RB, TB>::tma_setup(Ctx& c) {
 #define KF_PLAN_F1024 1024, 64, 16, KF_F1024_R1, KF_F1024_R2
 #endif
 
+// Launcher of resident_kernel<T, P, CS, MINB> (one cluster of CS CTAs per environment)
+template <typename T, class P, int CS, int MINB> struct Resident {
+  using C = kf::Cx<T>;
+  static cudaError_t prepare() {
+    cudaError_t e = cudaFuncSetAttribute(kf::resident_kernel<T, P, CS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)kf::ResidentSmem<T, P, CS>::bytes());
+    return e;
+  }
+  static cudaError_t launch(const Ctx& c, void* omega_user, const void* G, int B, int n_steps, cudaStream_t s) {
+    kf::ResidentArgs<T> a;
+    a.omega = (C*)omega_user;
+    a.G = (const C*)G;
+    a.tw = (const C*)c.tw;
+    for (int k = 0; k < 5; ++k) {
+      a.beta[k] = (T)kBeta[k];
+      a.gdt[k] = (T)(kGamma[k] * c.cfg.dt);                                     // base.py:55
+      a.munu[k] = (T)(0.5 * c.cfg.dt * (kAlpha[k + 1] - kAlpha[k]) * c.cfg.nu);  // base.py:54, kolmogorov.py:209-220
+    }
+    a.scale = (T)(1.0 / ((double)P::L * (double)P::L));
+    a.dealias = c.cfg.dealias;
+    a.n_steps = n_steps;
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)B * CS);
+    lc.blockDim = dim3(256);
+    lc.dynamicSmemBytes = kf::ResidentSmem<T, P, CS>::bytes();
+    lc.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    lc.attrs = at;
+    lc.numAttrs = CS > 1 ? 1 : 0;
+    return cudaLaunchKernelEx(&lc, kf::resident_kernel<T, P, CS, MINB>, a);
+  }
+  static void attach(Ops& o) {
+    o.resident_prepare = prepare;
+    o.resident = launch;
+    o.resident_cluster = CS;
+  }
+};
+
+template <class R> Ops with_resident(Ops o) {
+  R::attach(o);
+  return o;
+}
+
 const Ops* find_ops(int dtype, int N) {
   using kf::Plan;
-  static const Ops f64_[] = {Impl<float, Plan<64, 8, 8, 8>, 16, 16>::make()};
+  static const Ops f64_[] = {with_resident<Resident<float, Plan<64, 8, 8, 8>, 1, 2>>(Impl<float, Plan<64, 8, 8, 8>, 16, 16>::make())};
   static const Ops f128[] = {Impl<float, Plan<128, 8, 16, 8>, KF_CFG_F128>::make()};
   static const Ops f256[] = {Impl<float, Plan<KF_PLAN_F256>, KF_CFG_F256>::make()};
   static const Ops f512[] = {Impl<float, Plan<512, 32, 8, 8, 8>, 8, 4>::make()};
   static const Ops f1024[] = {Impl<float, Plan<KF_PLAN_F1024>, KF_CFG_F1024>::make()};
-  static const Ops d64[] = {Impl<double, Plan<64, 8, 8, 8>, 16, 16>::make()};
+  static const Ops d64[] = {with_resident<Resident<double, Plan<64, 8, 8, 8>, 1, 1>>(Impl<double, Plan<64, 8, 8, 8>, 16, 16>::make())};
   static const Ops d128[] = {KF_IMPL_D128::make()};
   static const Ops d256[] = {Impl<double, Plan<KF_PLAN_D256>, KF_CFG_D256>::make()};
   static const Ops d512[] = {KF_IMPL_D512::make()};
@@ -391,8 +459,23 @@ void enqueue_rk_step(Ctx& c, int nb, cudaStream_t s) {
   }
 }
 
-int build_graph(Ctx& c) {
-  if (c.graph) return 0;
+void drop_graphs(Ctx& c) {
+  for (int i = 0; i < Ctx::kGraphs; ++i) {
+    if (c.graph[i]) cudaGraphExecDestroy(c.graph[i]);
+    c.graph[i] = nullptr;
+    c.graph_nb[i] = 0;
+  }
+}
+
+// graph of 4 RK steps on nb environments of the lane's workspace; *out = nullptr if no slot is free (direct launches)
+int build_graph(Ctx& c, int nb, cudaGraphExec_t* out) {
+  *out = nullptr;
+  int slot = -1;
+  for (int i = 0; i < Ctx::kGraphs; ++i) {
+    if (c.graph[i] && c.graph_nb[i] == nb) { *out = c.graph[i]; return 0; }
+    if (!c.graph[i] && slot < 0) slot = i;
+  }
+  if (slot < 0) return 0;
   const int steps = 4;
   cudaGraph_t g = nullptr;
   // capture on a private stream (the caller's may be the legacy default stream, which cannot capture)
@@ -400,15 +483,16 @@ int build_graph(Ctx& c) {
   KF_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
   cudaError_t ce = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
   if (ce == cudaSuccess) {
-    for (int i = 0; i < steps; ++i) enqueue_rk_step(c, c.chunk, cs);
+    for (int i = 0; i < steps; ++i) enqueue_rk_step(c, nb, cs);
     ce = cudaStreamEndCapture(cs, &g);
   }
   cudaStreamDestroy(cs);
   if (ce != cudaSuccess) return fail(std::string("graph capture: ") + cudaGetErrorString(ce));
-  cudaError_t e = cudaGraphInstantiate(&c.graph, g, 0);
+  cudaError_t e = cudaGraphInstantiate(&c.graph[slot], g, 0);
   cudaGraphDestroy(g);
   if (e != cudaSuccess) return fail(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
-  c.graph_steps = steps;
+  c.graph_nb[slot] = nb;
+  *out = c.graph[slot];
   return 0;
 }
 
@@ -417,21 +501,20 @@ int build_graph(Ctx& c) {
 // (fields must be current on entry, are current on exit)
 int run_rk_steps(Ctx* const* L, const int* nb, const cudaStream_t* ls, int nl, int n) {
   int done = 0;
-  bool use_graph[2] = {false, false};
+  cudaGraphExec_t gx[2] = {nullptr, nullptr};
   bool any_graph = false;
   for (int l = 0; l < nl; ++l) {
-    if (nb[l] > 0 && L[l]->cfg.use_graph && nb[l] == L[l]->chunk && n >= 8) {
-      if (int rc = build_graph(*L[l])) return rc;
-      use_graph[l] = true;
-      any_graph = true;
+    if (nb[l] > 0 && L[l]->cfg.use_graph && n >= 8) {
+      if (int rc = build_graph(*L[l], nb[l], &gx[l])) return rc;
+      any_graph = any_graph || gx[l] != nullptr;
     }
   }
   const int gsteps = 4;
   while (any_graph && n - done >= gsteps) {
     for (int l = 0; l < nl; ++l) {
       if (nb[l] <= 0) continue;
-      if (use_graph[l]) {
-        KF_CUDA(cudaGraphLaunch(L[l]->graph, ls[l]));
+      if (gx[l]) {
+        KF_CUDA(cudaGraphLaunch(gx[l], ls[l]));
       } else {
         for (int i = 0; i < gsteps; ++i) enqueue_rk_step(*L[l], nb[l], ls[l]);
       }
@@ -484,15 +567,47 @@ int drive(Ctx& c, void* omega, const void* actions, void* traj, int n_outer, int
     KF_CUDA(cudaMemsetAsync(c.acc, 0, sizeof(double) * 4 * (size_t)B * n_outer, s));
     if (obs_dev) KF_CUDA(cudaMemsetAsync(obs_dev, 0, real * (size_t)B * nobs2, s));
   }
+  if (c.resident_on && !c.ctrl_on) {
+    // On-chip-resident path: the whole batch advances in place (user layout) inside ONE kernel per block of n_inner
+    // RK steps; the chunk workspace only serves the reward / observation reductions of the snapshots.
+    c.ops->forcing_to(c, c.Gfull, B, actions, s);
+    c.launches += 1;
+    for (int j = 0; j < n_outer; ++j) {
+      KF_CUDA(c.ops->resident(c, omega, c.Gfull, B, n_inner, s));
+      c.launches += 1;
+      if (traj)
+        KF_CUDA(cudaMemcpy2DAsync((char*)traj + el * user_env * j, el * user_env * n_outer, omega, el * user_env,
+                                  el * user_env, B, cudaMemcpyDeviceToDevice, s));
+      if (want_obs) {
+        for (int b0 = 0; b0 < B; b0 += c.chunk) {
+          const int nb = B - b0 < c.chunk ? B - b0 : c.chunk;
+          c.ops->import_(c, nb, (const char*)omega + el * user_env * b0, user_env, s);
+          c.ops->col(c, nb, stage_of(c, 0), kf::kColInit, s);
+          c.ops->obs(c, nb, c.acc + 4 * ((size_t)b0 * n_outer + j), 4 * (size_t)n_outer,
+                     obs_dev ? (char*)obs_dev + real * (size_t)b0 * nobs2 : nullptr, 1.0 / n_outer, s);
+          c.launches += 3;
+        }
+      }
+    }
+    if (want_obs) {
+      c.ops->finalize(c, n_outer, tke_dev, nonf_dev, s);
+      c.launches += 1;
+    }
+    KF_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (nl == 2) {
     KF_CUDA(cudaEventRecord(c.ev_fork, s));
     KF_CUDA(cudaStreamWaitEvent(c.s2, c.ev_fork, 0));
   }
   for (int g0 = 0; g0 < B; g0 += nl * c.chunk) {
     int b0[2], nb[2];
+    // a last round with fewer than lanes x chunk environments is split evenly between the lanes
+    const int left = B - g0;
+    const int per = (nl == 2 && left < 2 * c.chunk) ? (left + 1) / 2 : c.chunk;
     for (int l = 0; l < nl; ++l) {
-      b0[l] = g0 + l * c.chunk;
-      nb[l] = B - b0[l] < c.chunk ? B - b0[l] : c.chunk;
+      b0[l] = g0 + l * per;
+      nb[l] = B - b0[l] < per ? B - b0[l] : per;
       if (nb[l] <= 0) { nb[l] = 0; continue; }
       char* om = (char*)omega + el * user_env * b0[l];
       c.ops->import_(*L[l], nb[l], om, user_env, ls[l]);
@@ -559,10 +674,10 @@ void free_all(Ctx& c) {
   if (c.ev_join) cudaEventDestroy(c.ev_join);
   void* ptrs[] = {c.wmain, c.wnyq, c.hmain, c.hnyq, c.G, c.fld, c.advx, c.tw, c.F, c.C,
                   c.acc, c.d_omega, c.d_act, c.d_obs, c.d_tke, c.d_nonf, c.ctrl_owner ? c.ctrl_main : nullptr,
-                  c.ctrl_owner ? c.ctrl_nyq : nullptr};
+                  c.ctrl_owner ? c.ctrl_nyq : nullptr, c.Gfull};
   for (void* p : ptrs)
     if (p) cudaFree(p);
-  if (c.graph) cudaGraphExecDestroy(c.graph);
+  drop_graphs(c);
 }
 
 // one lane: chunk-sized workspace, twiddles, TMA descriptors
@@ -594,6 +709,7 @@ int setup_lane(Ctx& c, const kf_config* cfg, const Ops* ops, int chunk) {
     KF_CUDA(cudaMemcpy(c.tw, t64.data(), el * c.N, cudaMemcpyHostToDevice));
   }
   if (const char* e = std::getenv("KF_PDL")) c.pdl = std::atoi(e) != 0;
+  if (const char* e = std::getenv("KF_L2_HINTS")) c.l2_hints = std::atoi(e);
   if (!std::getenv("KF_NO_TMA")) return ops->tma_setup(c);
   return 0;
 }
@@ -669,7 +785,17 @@ int kf_create(kf_handle* out, const kf_config* cfg) {
   cudaError_t pe = ops->prepare();
   if (pe != cudaSuccess) rc = fail(std::string("kernel attribute setup: ") + cudaGetErrorString(pe));
   if (!rc) rc = setup_lane(h->c, cfg, ops, chunk);
-  if (!rc && two_lanes) {
+  if (!rc && ops->resident) {
+    // on-chip-resident stepping is the default where a grid fits (64^2); KF_RESIDENT=0 selects the two-kernel path
+    const char* e = std::getenv("KF_RESIDENT");
+    if (!(e && e[0] == '0')) {
+      cudaError_t re = ops->resident_prepare();
+      if (re != cudaSuccess) rc = fail(std::string("resident kernel set-up: ") + cudaGetErrorString(re));
+      if (!rc) rc = dev_alloc(h->c, &h->c.Gfull, ops->elem * (size_t)cfg->B * (cfg->N / 2 + 1));
+      if (!rc) h->c.resident_on = true;
+    }
+  }
+  if (!rc && two_lanes && !h->c.resident_on) {
     Ctx& c = h->c;
     c.lane2 = new Ctx();
     rc = setup_lane(*c.lane2, cfg, ops, chunk);
@@ -887,12 +1013,8 @@ int kf_set_control_field(kf_handle h, const void* control_hat_host) {
   Ctx& c = h->c;
   DeviceGuard guard(c.cfg.device);
   KF_CUDA(cudaDeviceSynchronize());
-  for (Ctx* l : {&c, c.lane2}) {  // captured graphs hold the old kernel arguments
-    if (l && l->graph) {
-      cudaGraphExecDestroy(l->graph);
-      l->graph = nullptr;
-    }
-  }
+  for (Ctx* l : {&c, c.lane2})  // captured graphs hold the old kernel arguments
+    if (l) drop_graphs(*l);
   if (!control_hat_host) {
     for (Ctx* l : {&c, c.lane2})
       if (l) l->ctrl_on = false;

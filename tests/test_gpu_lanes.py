@@ -14,7 +14,10 @@ pytestmark = pytest.mark.gpu
 
 
 def _with_lanes(value, fn):
-    old = os.environ.get("KF_LANES")
+    """Run fn with KF_LANES forced and the on-chip-resident path off (these tests are about the lanes of the
+    two-kernel path; 64^2 would otherwise take the resident kernel, which has no lanes)."""
+    old, old_res = os.environ.get("KF_LANES"), os.environ.get("KF_RESIDENT")
+    os.environ["KF_RESIDENT"] = "0"
     if value is None:
         os.environ.pop("KF_LANES", None)
     else:
@@ -22,10 +25,11 @@ def _with_lanes(value, fn):
     try:
         return fn()
     finally:
-        if old is None:
-            os.environ.pop("KF_LANES", None)
-        else:
-            os.environ["KF_LANES"] = old
+        for key, val in (("KF_LANES", old), ("KF_RESIDENT", old_res)):
+            if val is None:
+                os.environ.pop(key, None)
+            else:
+                os.environ[key] = val
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
