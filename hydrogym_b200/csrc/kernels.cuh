@@ -474,16 +474,19 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) row_kernel(StageArgs<T> 
   for (int m = 0; m < E / 2; ++m) {
     const int k = t + TPF * m;
     if (a.dealias && k >= km) continue;  // masked by the column kernel anyway: never read, so never written
+    Cx<T> r0, r1;
     if (k == 0) {
       const Cx<T> wn = ex1.load(MH);
-      stc(o0, mk<T>(v[m].x, wn.x));
-      stc(o1, mk<T>(v[m].y, wn.y));
+      r0 = mk<T>(v[m].x, wn.x);
+      r1 = mk<T>(v[m].y, wn.y);
     } else {
       const Cx<T> wm = ex1.load(M - k);
       const Cx<T> s = add_conj(v[m], wm), d = sub_conj(v[m], wm);
-      stc(o0 + k, (T)0.5 * s);
-      stc(o1 + k, mk<T>((T)0.5 * d.y, (T)-0.5 * d.x));
+      r0 = (T)0.5 * s;
+      r1 = mk<T>((T)0.5 * d.y, (T)-0.5 * d.x);
     }
+    stc(o0 + k, r0);
+    stc(o1 + k, r1);
   }
 }
 

@@ -73,6 +73,7 @@ struct Ops {
   cudaError_t (*resident_prepare)() = nullptr;
   cudaError_t (*resident)(const struct Ctx&, void* omega_user, const void* G, int B, int n_steps, cudaStream_t) = nullptr;
   int resident_cluster = 0;
+  bool resident_default = false;  // taken unless KF_RESIDENT=0; otherwise only with KF_RESIDENT=1
 };
 
 struct Ctx {
@@ -401,26 +402,33 @@ template <typename T, class P, int CS, int MINB> struct Resident {
     lc.numAttrs = CS > 1 ? 1 : 0;
     return cudaLaunchKernelEx(&lc, kf::resident_kernel<T, P, CS, MINB>, a);
   }
-  static void attach(Ops& o) {
+  static void attach(Ops& o, bool by_default) {
     o.resident_prepare = prepare;
     o.resident = launch;
     o.resident_cluster = CS;
+    o.resident_default = by_default;
   }
 };
 
-template <class R> Ops with_resident(Ops o) {
-  R::attach(o);
+template <class R> Ops with_resident(Ops o, bool by_default) {
+  R::attach(o, by_default);
   return o;
 }
 
 const Ops* find_ops(int dtype, int N) {
   using kf::Plan;
-  static const Ops f64_[] = {with_resident<Resident<float, Plan<64, 8, 8, 8>, 1, 2>>(Impl<float, Plan<64, 8, 8, 8>, 16, 16>::make())};
-  static const Ops f128[] = {Impl<float, Plan<128, 8, 16, 8>, KF_CFG_F128>::make()};
+  // on-chip-resident kernels (resident.cuh): 64^2 one CTA per environment (default path); 128^2 / 256^2 fp32 as
+  // clusters of 2 / 8 CTAs exchanging through distributed shared memory (opt-in: KF_RESIDENT=1)
+  static const Ops f64_[] = {with_resident<Resident<float, Plan<64, 8, 8, 8>, 1, 2>>(Impl<float, Plan<64, 8, 8, 8>, 16, 16>::make(), true)};
+  static const Ops f128[] = {with_resident<Resident<float, Plan<128, 8, 16, 8>, 2, 1>>(Impl<float, Plan<128, 8, 16, 8>, KF_CFG_F128>::make(), false)};
+#if KF_F256_TPF == 16
+  static const Ops f256[] = {with_resident<Resident<float, Plan<256, 16, 16, 16>, 8, 1>>(Impl<float, Plan<KF_PLAN_F256>, KF_CFG_F256>::make(), false)};
+#else
   static const Ops f256[] = {Impl<float, Plan<KF_PLAN_F256>, KF_CFG_F256>::make()};
+#endif
   static const Ops f512[] = {Impl<float, Plan<512, 32, 8, 8, 8>, 8, 4>::make()};
   static const Ops f1024[] = {Impl<float, Plan<KF_PLAN_F1024>, KF_CFG_F1024>::make()};
-  static const Ops d64[] = {with_resident<Resident<double, Plan<64, 8, 8, 8>, 1, 1>>(Impl<double, Plan<64, 8, 8, 8>, 16, 16>::make())};
+  static const Ops d64[] = {with_resident<Resident<double, Plan<64, 8, 8, 8>, 1, 1>>(Impl<double, Plan<64, 8, 8, 8>, 16, 16>::make(), true)};
   static const Ops d128[] = {KF_IMPL_D128::make()};
   static const Ops d256[] = {Impl<double, Plan<KF_PLAN_D256>, KF_CFG_D256>::make()};
   static const Ops d512[] = {KF_IMPL_D512::make()};
@@ -709,7 +717,10 @@ int setup_lane(Ctx& c, const kf_config* cfg, const Ops* ops, int chunk) {
     KF_CUDA(cudaMemcpy(c.tw, t64.data(), el * c.N, cudaMemcpyHostToDevice));
   }
   if (const char* e = std::getenv("KF_PDL")) c.pdl = std::atoi(e) != 0;
-  if (const char* e = std::getenv("KF_L2_HINTS")) c.l2_hints = std::atoi(e);
+  // L2-blocked stepping (a chunk smaller than the batch lives in L2 by design): stream omega_hat / h with the
+  // evict_first policy so the fields and advection rows keep the cache (+1 % at 256^2 x 256 fp32, profiles/r2_sweep_*)
+  c.l2_hints = (chunk < cfg->B) ? 1 : 0;
+  if (const char* e = std::getenv("KF_L2_HINTS")) c.l2_hints = std::atoi(e) & 1;
   if (!std::getenv("KF_NO_TMA")) return ops->tma_setup(c);
   return 0;
 }
@@ -788,7 +799,7 @@ int kf_create(kf_handle* out, const kf_config* cfg) {
   if (!rc && ops->resident) {
     // on-chip-resident stepping is the default where a grid fits (64^2); KF_RESIDENT=0 selects the two-kernel path
     const char* e = std::getenv("KF_RESIDENT");
-    if (!(e && e[0] == '0')) {
+    if (e ? e[0] == '1' : ops->resident_default) {
       cudaError_t re = ops->resident_prepare();
       if (re != cudaSuccess) rc = fail(std::string("resident kernel set-up: ") + cudaGetErrorString(re));
       if (!rc) rc = dev_alloc(h->c, &h->c.Gfull, ops->elem * (size_t)cfg->B * (cfg->N / 2 + 1));

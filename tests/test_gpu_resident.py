@@ -25,9 +25,11 @@ def _resident(on, fn):
 
 
 @pytest.mark.parametrize("dealias", [False, True])
-@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-11), (torch.float32, 2e-5)])
-def test_resident_rk_steps_match_oracle(dtype, tol, dealias):
-    N, B, steps = 64, 5, 20
+@pytest.mark.parametrize("N,steps,dtype,tol", [(64, 20, torch.float64, 1e-11), (64, 20, torch.float32, 2e-5),
+                                               (128, 6, torch.float32, 2e-5), (256, 3, torch.float32, 2e-5)])
+def test_resident_rk_steps_match_oracle(N, steps, dtype, tol, dealias):
+    """64^2: one CTA per environment; 128^2 / 256^2 fp32: clusters of 2 / 8 CTAs over distributed shared memory."""
+    B = 5
     npdt = np.float64 if dtype == torch.float64 else np.float32
     ref = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=npdt, dealias=dealias)
     w0 = random_states(ref, B, seed=21).astype(orc._ctype(npdt))

@@ -4,7 +4,7 @@ variants/lib_*.so (KF_LIB) in its own interpreter; `--here` runs the settings ag
 import glob, os, subprocess, sys
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, root)
-SETTINGS = [(0, 1, 0), (0, 3, 0), (0, 1, 1), (0, 3, 1), (64, 1, 1), (37, 1, 1)]  # (chunk, KF_L2_HINTS, KF_COL_PER_SM)
+SETTINGS = [(0, 0, 0), (0, 1, 0), (37, 1, 0), (0, 1, 1)]  # (chunk, KF_L2_HINTS, KF_RESIDENT)
 
 
 def here():
@@ -13,7 +13,7 @@ def here():
     N, B = 256, 256
     for chunk, hints, colsm in SETTINGS:
         os.environ["KF_L2_HINTS"] = str(hints)
-        os.environ["KF_COL_PER_SM"] = str(colsm)
+        os.environ["KF_RESIDENT"] = str(colsm)
         st = KolmogorovStepper(grid_size=(N, N), Re=1000, num_envs=B, dtype=torch.float32, device="cuda:0", chunk=chunk)
         g = torch.Generator(device="cuda").manual_seed(0)
         w = torch.randn(B, N, N // 2 + 1, dtype=torch.complex64, device="cuda", generator=g)
@@ -28,8 +28,9 @@ def here():
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / 600
         C = N * (N // 2 + 1) * 8
-        print(f"  chunk {st.chunk:3d} (asked {chunk:2d}) lanes {st.lanes} hints {hints} col/SM {colsm}: {ms:.4f} ms/RK step  "
-              f"frac {70 * C * B / (ms * 1e-3) / 1e9 / 6552.6:.3f}  finite={bool(torch.isfinite(torch.view_as_real(w)).all())}",
+        mc, mr = st.profile_kernels(20)
+        print(f"  chunk {st.chunk:3d} (asked {chunk:2d}) lanes {st.lanes} hints {hints} resident(cluster of 8) {colsm}: {ms:.4f} ms/RK step  "
+              f"frac {70 * C * B / (ms * 1e-3) / 1e9 / 6552.6:.3f}  finite={bool(torch.isfinite(torch.view_as_real(w)).all())}  col {mc*1e3:.1f} us row {mr*1e3:.1f} us",
               flush=True)
         st.close()
 
