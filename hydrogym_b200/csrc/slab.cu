@@ -105,15 +105,21 @@ __global__ void slab_barrier_kernel(BarrierArgs a) {
   __syncthreads();
 }
 
-template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS, int CMINB = 2, int TWS = 0> struct SlabImpl {
+template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS, int CMINB = 2, int TWS = 0, bool LEAN = false>
+struct SlabImpl {
   static_assert(PH::L * 2 == P::L, "the row kernel's plan is half the grid size");
   using C = kf::Cx<T>;
   using C2 = kf::Cx<typename kf::PairOf<T>::type>;
   static constexpr int N = P::L, MH = N / 2;
-  static size_t smem(int groups) { return sizeof(C2) * groups * kf::slab_exchange_elems<N>() + sizeof(C) * (size_t)N; }
+  // LEAN (fp64 at 8192 points): split exchange + twiddles from global memory in the one-CTA packed-column kernel and
+  // the observation kernel, whose whole-transform buffers would not fit 227 KB otherwise
+  static size_t smem(int groups) {
+    return LEAN ? sizeof(C) * groups * kf::slab_exchange_elems<N>()
+                : sizeof(C2) * groups * kf::slab_exchange_elems<N>() + sizeof(C) * (size_t)N;
+  }
 
   static size_t smem_scalar() { return kf::slab_scalar_smem_bytes<T, N, GROUPS, TWS>(); }
-  static size_t smem_obs() { return sizeof(C) * (RGROUPS * kf::slab_exchange_elems<N>() + (size_t)N); }
+  static size_t smem_obs() { return sizeof(C) * (RGROUPS * kf::slab_exchange_elems<N>() + (LEAN ? 0 : (size_t)N)); }
 
   static cudaError_t prepare() {
     cudaError_t e;
@@ -122,10 +128,10 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS, i
   if (e != cudaSuccess) return e;
     KF_ATTR((kf::slab_col_scalar_kernel<T, P, GROUPS, kf::kSlabStage, CMINB, TWS>), smem_scalar())
     KF_ATTR((kf::slab_col_scalar_kernel<T, P, GROUPS, kf::kSlabInit, CMINB, TWS>), smem_scalar())
-    KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabStage, true, 1>), smem(1))
-    KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabInit, true, 1>), smem(1))
+    KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabStage, true, 1, LEAN>), smem(1))
+    KF_ATTR((kf::slab_col_kernel<T, P, 1, kf::kSlabInit, true, 1, LEAN>), smem(1))
     KF_ATTR((kf::slab_row_half_kernel<T, PH, HGROUPS, 2>), (kf::slab_half_smem_bytes<T, PH::L, HGROUPS>()))
-    KF_ATTR((kf::slab_row_obs_kernel<T, P, RGROUPS>), smem_obs())
+    KF_ATTR((kf::slab_row_obs_kernel<T, P, RGROUPS, LEAN>), smem_obs())
 #undef KF_ATTR
     return cudaSuccess;
   }
@@ -160,7 +166,7 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS, i
     if (c.rank == 0) {
       cudaEventRecord(c.ev_fork, s);
       cudaStreamWaitEvent(c.side, c.ev_fork, 0);
-      kf::slab_col_kernel<T, P, 1, MODE, true, 1><<<1, P::TPF, smem(1), c.side>>>(a);
+      kf::slab_col_kernel<T, P, 1, MODE, true, 1, LEAN><<<1, P::TPF, smem(1), c.side>>>(a);
       cudaEventRecord(c.ev_join, c.side);
     }
     main_k<<<wave(c, main_k, threads, smem_scalar(), c.Q / GROUPS), threads, smem_scalar(), s>>>(a);
@@ -215,7 +221,7 @@ template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS, i
     kf::SlabArgs<T> a = args(c);
     a.fx = (const C*)(fld_recv ? fld_recv : c.own_fld);
     const int st = N / c.cfg.obs_size;
-    kf::slab_row_obs_kernel<T, P, RGROUPS><<<c.X / RGROUPS, P::TPF * RGROUPS, smem_obs(), s>>>(
+    kf::slab_row_obs_kernel<T, P, RGROUPS, LEAN><<<c.X / RGROUPS, P::TPF * RGROUPS, smem_obs(), s>>>(
         a, acc, (T*)obs_dev, c.cfg.obs_size, st, st, (T)obs_w);
   }
 
@@ -270,12 +276,16 @@ const SlabOps* find_slab_ops(int dtype, int N) {
   static const SlabOps d256 = SlabImpl<double, Plan<256, 16, 16, 16>, 8, 8, Plan<128, 8, 16, 8>, 16>::make();
   static const SlabOps d1024 = SlabImpl<double, Plan<1024, 64, 16, 4, 16>, 2, 2, Plan<512, 32, 8, 8, 8>, 4>::make();
   static const SlabOps d4096 = SlabImpl<double, Plan<4096, 256, 16, 16, 16>, 1, 1, Plan<2048, 128, 16, 8, 16>, 1>::make();
+  // fp64 at 8192 points: one transform per CTA everywhere (139 KB exchange buffers), twiddles of the column kernels
+  // through L1, LEAN packed-column / observation kernels
+  static const SlabOps d8192 =
+      SlabImpl<double, Plan<8192, 512, 16, 16, 2, 16>, 1, 1, Plan<4096, 256, 16, 16, 16>, 1, 1, 0, true>::make();
   const bool f = dtype == KF_F32;
   switch (N) {
     case 256: return f ? &f256 : &d256;
     case 1024: return f ? &f1024 : &d1024;
     case 4096: return f ? &f4096 : &d4096;
-    case 8192: return f ? &f8192 : nullptr;
+    case 8192: return f ? &f8192 : &d8192;
     default: return nullptr;
   }
 }
@@ -330,7 +340,7 @@ int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks) {
   if (cfg->N != cfg->M) return fail("kf_slab_create: only square grids are supported (N == M)");
   if (cfg->dtype != KF_F32 && cfg->dtype != KF_F64) return fail("kf_slab_create: dtype must be KF_F32 or KF_F64");
   const SlabOps* ops = find_slab_ops(cfg->dtype, cfg->N);
-  if (!ops) return fail("kf_slab_create: grid size must be 256, 1024 or 4096 (fp32, fp64) or 8192 (fp32)");
+  if (!ops) return fail("kf_slab_create: grid size must be 256, 1024, 4096 or 8192");
   if (nranks < 1 || (nranks & (nranks - 1)) != 0) return fail("kf_slab_create: nranks must be a power of two");
   if (rank < 0 || rank >= nranks) return fail("kf_slab_create: rank out of range");
   if (cfg->N / 2 / nranks < 8) return fail("kf_slab_create: need at least 8 packed columns per rank");

@@ -15,6 +15,8 @@
 // Column 0 of the packed x-space layout carries ky = 0 and ky = M/2 together (see kernels.cuh); it lives on
 // rank 0 and is handled by the SPECIAL instance of slab_col_kernel (one CTA).
 #pragma once
+#include <type_traits>
+
 #include "kernels.cuh"
 
 namespace kf {
@@ -96,7 +98,10 @@ template <typename T, int N> __device__ __forceinline__ T wave_of(int kx) { retu
 // thread t holds rows {t + TPF*m}.  grid = Q / GROUPS (normal) or 1 CTA with GROUPS = 1 (SPECIAL, rank 0,
 // packed column 0 = ky 0 and ky M/2).  The normal instance computes global column 0 too but discards it.
 // ---------------------------------------------------------------------------
-template <typename T, class P, int GROUPS, int MODE, bool SPECIAL, int MINB>
+// LEAN (fp64 at 8192 points, where a whole lane-paired transform plus the twiddle table would need 409 KB): the
+// lane-paired exchange goes through lane values in two rounds (RowExSplit, N x 16 B) and the twiddles are read from
+// global memory -- 139 KB of shared memory instead.
+template <typename T, class P, int GROUPS, int MODE, bool SPECIAL, int MINB, bool LEAN = false>
 __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs<T> a) {
   using L2 = typename PairOf<T>::type;
   constexpr int N = P::L, E = P::E, TPF = P::TPF, MH = N / 2;
@@ -104,12 +109,16 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
   static_assert(!SPECIAL || GROUPS == 1, "the packed column is one CTA");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int g = threadIdx.x / TPF, t0 = threadIdx.x % TPF;
-  unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<L2>);
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
+  unsigned char* s_g = smem_raw + (size_t)g * EXN * (LEAN ? sizeof(Cx<T>) : sizeof(Cx<L2>));
+  const Cx<T>* s_tw = LEAN ? a.tw : reinterpret_cast<const Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
   RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
-  RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
-  for (int i = threadIdx.x; i < N; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
-  __syncthreads();
+  typename std::conditional<LEAN, RowExSplit<L2, TPF>, RowEx<L2, TPF>>::type ex2{
+      reinterpret_cast<typename std::conditional<LEAN, L2, Cx<L2>>::type*>(s_g)};
+  if constexpr (!LEAN) {
+    Cx<T>* tw_w = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
+    for (int i = threadIdx.x; i < N; i += TPF * GROUPS) tw_w[i] = ldc(a.tw + i);
+    __syncthreads();
+  }
 
   // persistent CTAs (the host launches at most one wave): the twiddle table is staged once per CTA
   const int ncb = SPECIAL ? 1 : a.Q / GROUPS;
@@ -482,21 +491,24 @@ __global__ void __launch_bounds__(PH::TPF* GROUPS, MINB) slab_row_half_kernel(Sl
 // _trajectory_mean_obs kolmogorov.py:426-446): acc[4] += (sum u, sum v, sum u^2, sum v^2) over the local
 // rows; |velocity| at the probes that fall on local rows is added to obs with weight obs_w.  The host sums
 // acc and obs over the ranks.  One row per group; grid = X / GROUPS.
-template <typename T, class P, int GROUPS>
+template <typename T, class P, int GROUPS, bool LEAN = false>
 __global__ void __launch_bounds__(P::TPF* GROUPS) slab_row_obs_kernel(SlabArgs<T> a, double* acc, T* obs, int nobs,
                                                                       int sx, int sy, T obs_w) {
   constexpr int M = P::L, E = P::E, TPF = P::TPF;
   constexpr size_t EXN = slab_exchange_elems<M>();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
-  Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw) + (size_t)GROUPS * EXN;
+  const Cx<T>* s_tw = LEAN ? a.tw : reinterpret_cast<const Cx<T>*>(smem_raw) + (size_t)GROUPS * EXN;
   RowEx<T, TPF> ex{reinterpret_cast<Cx<T>*>(smem_raw) + (size_t)g * EXN};
   const int xl = blockIdx.x * GROUPS + g;
   const int x = a.x0 + xl;
   const int Q = a.Q, lgQ = a.lgQ;
 
-  for (int i = threadIdx.x; i < M; i += TPF * GROUPS) s_tw[i] = ldc(a.tw + i);
-  __syncthreads();
+  if constexpr (!LEAN) {  // LEAN: twiddles straight from global memory (no room for the table beside the exchange)
+    Cx<T>* tw_w = reinterpret_cast<Cx<T>*>(smem_raw) + (size_t)GROUPS * EXN;
+    for (int i = threadIdx.x; i < M; i += TPF * GROUPS) tw_w[i] = ldc(a.tw + i);
+    __syncthreads();
+  }
 
   const size_t roff = (size_t)xl * Q, blk = a.fblk;
   // one scalar transform of u_hat + i v_hat (planes 0 and 2): real part u, imaginary part v

@@ -13,6 +13,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p"])
     ap.add_argument("--dt", type=float, default=0.0, help="0 = CFL-safe default 0.8/N (1e-4 at 8192)")
+    ap.add_argument("--dtype", default="fp32", choices=["fp32", "fp64"])
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -22,9 +23,11 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N = a.grid
     dt = a.dt if a.dt > 0 else 0.8 / N  # u ~ 1: CFL = u dt N / (2 pi) ~ 0.13
-    sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float32, device=f"cuda:{local}", dealias=True, dt=dt, exchange=a.exchange)
+    rd = torch.float32 if a.dtype == "fp32" else torch.float64
+    cd = torch.complex64 if a.dtype == "fp32" else torch.complex128
+    sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=rd, device=f"cuda:{local}", dealias=True, dt=dt, exchange=a.exchange)
     g = torch.Generator(device="cuda").manual_seed(0)
-    w = torch.randn(N, N // 2 + 1, dtype=torch.complex64, device="cuda", generator=g)
+    w = torch.randn(N, N // 2 + 1, dtype=cd, device="cuda", generator=g)
     p = torch.fft.fftfreq(N, 1.0 / N, device="cuda")[:, None]; q = torch.arange(N // 2 + 1, device="cuda")[None, :]
     w = w * torch.exp(-(p * p + q * q) / 64.0) * N * N * 0.5
     sl.set_state(w, None)
@@ -40,9 +43,9 @@ def main():
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     obs, tke = sl.reward_obs()
-    C = N * (N // 2 + 1) * 8
+    C = N * (N // 2 + 1) * (8 if a.dtype == "fp32" else 16)
     if rank == 0:
-        print(json.dumps({"metric": "RK steps/s (single grid, slab-decomposed)", "grid": N, "n_gpus": world, "exchange": a.exchange, "dt": dt, "rk_steps_run": a.steps + a.warmup,
+        print(json.dumps({"metric": "RK steps/s (single grid, slab-decomposed)", "grid": N, "dtype": a.dtype, "n_gpus": world, "exchange": a.exchange, "dt": dt, "rk_steps_run": a.steps + a.warmup,
                           "ms_per_rk_step": float(ms), "value": 1e3 / float(ms), "unit": "RK steps/s",
                           "algorithmic_GBps_per_gpu": 70 * C / world / float(ms) / 1e6,
                           "a2a_bytes_per_gpu_per_step": 5 * 5 * C // world * (world - 1) // world,
