@@ -456,6 +456,31 @@ def slab_record(torch, dist, args, dev, rank, world, max_over_ranks, peak):
         sl.close()
     best = min(rec["exchanges"], key=lambda m: rec["exchanges"][m]["ms_per_rk_step"])
     rec.update({"exchange": best, "dt": dt, **rec["exchanges"][best]})
+    del w
+    # ---- the same grid in fp64 (peer-store exchange, fewer steps) ---------------------------------------------
+    try:
+        w64 = _device_random_states(torch, 1, N, torch.complex128, dev, seed=0, amp=0.5)[0]
+        sl = SlabKolmogorovSolver(grid_size=(N, N), Re=1000, dtype=torch.float64, device=dev, dt=dt, exchange="p2p")
+        sl.set_state(w64, None)
+        del w64
+        sl.rk_steps(2)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n64 = max(2, args.slab_steps // 4)
+        e0.record(torch.cuda.current_stream(dev))
+        sl.rk_steps(n64)
+        e1.record(torch.cuda.current_stream(dev))
+        torch.cuda.synchronize(dev)
+        ms = max_over_ranks(e0.elapsed_time(e1) / n64)
+        _, tke = sl.reward_obs()
+        rec["fp64"] = {"ms_per_rk_step": ms, "rk_steps_run": n64 + 2, "exchange": "p2p",
+                       "frac_of_70C_roofline": 70.0 * 2 * C / world / (ms * 1e-3) / 1e9 / peak,
+                       "finite": bool(torch.isfinite(tke).all()), "workspace_bytes_per_gpu": int(sl.workspace_bytes)}
+        sl.close()
+    except Exception as e:
+        rec["fp64"] = {"error": f"{type(e).__name__}: {e}"}
     return rec
 
 

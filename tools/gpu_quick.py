@@ -35,6 +35,8 @@ PRESETS = {
     "chunks": [(256, 256, "f32", 40, dict(chunk=c)) for c in (0, 16, 32, 37, 64, 74, 128)],
     "other": [(1024, 16, "f32", 10, {}), (512, 64, "f32", 10, {}), (64, 1024, "f32", 20, {}), (128, 1024, "f64", 10, {})],
     "nograph": [(256, 256, "f32", 40, dict(use_graph=False))],
+    "c1024": [(1024, 16, "f32", 10, dict(chunk=c)) for c in (0, 8, 4, 2)],
+    "d256": [(256, 256, "f64", 20, dict(chunk=c)) for c in (0, 128, 32, 16)],
     "dealias": [(256, 256, "f32", 40, dict(dealias=True))],
 }
 
