@@ -386,15 +386,35 @@ def extra_configs(torch, dev, world, max_over_ranks, peak):
     out = []
     for name, N, B, Re, dt_name, n_rk in (("configs[2] fp64", 256, 256, 1000.0, "fp64", 200),
                                           ("configs[1]", 128, 1024, 100.0, "fp32", 400),
-                                          ("configs[3]", 1024, 16, 1000.0, "fp32", 200)):
+                                          ("configs[3]", 1024, 16, 1000.0, "fp32", 200),
+                                          ("configs[0] grid (the reference's default 64^2), batched fp32", 64, 1024, 100.0, "fp32", 1000),
+                                          ("configs[0] grid, batched fp64", 64, 1024, 100.0, "fp64", 400),
+                                          ("configs[0]: 64^2 Re=100 single env fp64", 64, 1, 100.0, "fp64", 2000)):
         tdt = torch.float32 if dt_name == "fp32" else torch.float64
+        C = N * (N // 2 + 1) * 2 * (4 if dt_name == "fp32" else 8)
+        rec = {"config": name, "grid": N, "envs_per_gpu": B, "Re": Re, "dtype": dt_name, "dealias": False,
+               "rk_steps_timed": n_rk}
+        if N == 64:
+            # default path: the on-chip-resident kernel (one CTA per environment, csrc/resident.cuh); the two-kernel
+            # path (KF_RESIDENT=0) is timed beside it.  The resident kernel moves almost nothing through HBM, so its
+            # fraction of the 70C ALGORITHMIC roofline may exceed 1.
+            old = os.environ.get("KF_RESIDENT")
+            os.environ["KF_RESIDENT"] = "0"
+            try:
+                ms2 = max_over_ranks(time_rk_steps(torch, N, B, Re, tdt, dev, n_rk)[0])
+            finally:
+                if old is None:
+                    os.environ.pop("KF_RESIDENT", None)
+                else:
+                    os.environ["KF_RESIDENT"] = old
+            rec["two_kernel_path"] = {"ms_per_rk_step": ms2, "frac": 70.0 * C * B / (ms2 * 1e-3) / 1e9 / peak}
+            rec["path"] = "resident_kernel (on-chip, one CTA per environment)"
         ms, finite, chunk, lanes = time_rk_steps(torch, N, B, Re, tdt, dev, n_rk)
         ms = max_over_ranks(ms)
-        C = N * (N // 2 + 1) * 2 * (4 if dt_name == "fp32" else 8)
         gbs = 70.0 * C * B / (ms * 1e-3) / 1e9
-        out.append({"config": name, "grid": N, "envs_per_gpu": B, "Re": Re, "dtype": dt_name, "dealias": False,
-                    "rk_steps_timed": n_rk, "ms_per_rk_step": ms, "rk_steps_env_per_s": world * B / (ms * 1e-3),
+        rec.update({"ms_per_rk_step": ms, "rk_steps_env_per_s": world * B / (ms * 1e-3),
                     "whole_step": {"achieved": gbs, "frac": gbs / peak}, "finite": finite, "chunk": chunk, "lanes": lanes})
+        out.append(rec)
     return out
 
 
