@@ -82,9 +82,17 @@ template <int CS, typename V> __device__ __forceinline__ void st_rank(V* p, unsi
 template <typename T, class P, int CS> struct ResidentSmem {
   using L2 = typename PairOf<T>::type;
   static constexpr int N = P::L, MH = N / 2, MHc = MH / CS, Nc = N / CS;
-  static constexpr int KS = N + 4;    // column stride of the K-layout buffers (bank-conflict padding)
-  static constexpr int XS = MH + 1;   // row stride of FX
-  static constexpr int EXN = N + N / 16;  // padded private exchange buffer of one group
+  // Strides in elements.  64-bit shared accesses are served per HALF-warp, and with TPF = 8 a half-warp is two groups
+  // (two columns / two private exchange buffers): consecutive groups must sit 64 bytes apart modulo 128, i.e. the
+  // stride must be 8 modulo 16 elements (ncu: with N + 4 / N + N/16 every LDS.64 / STS.64 of the K phases and of the
+  // exchanges took 2x its ideal wavefronts and the kernel was bound by the shared-memory pipe at 80 %; fixing it took
+  // 64^2 x 1024 fp32 from 183 to 175 us per RK step).  fp64 elements are 16 bytes, one group per quarter-warp: the
+  // original strides are the better ones there (438 vs 456 us), so the padding depends on the element size.
+  static constexpr bool kF32 = sizeof(T) == 4;
+  static constexpr int KS = kF32 ? N + 8 : N + 4;  // column stride of the K-layout buffers
+  static constexpr int XS = MH + 1;   // row stride of FX (16-byte elements: one quarter-warp = one group, 8 distinct slots)
+  static constexpr int kExMin = N + N / 16;  // padded private exchange buffer of one group (RowEx::pad)
+  static constexpr int EXN = kF32 ? kExMin + ((8 - kExMin % 16) + 16) % 16 : kExMin;
   static constexpr int GROUPS = 256 / P::TPF;
   static_assert(GROUPS == MHc && 2 * GROUPS == Nc, "256 threads: one group per owned column and per owned row pair");
   static constexpr size_t kK = (size_t)MHc * KS * sizeof(Cx<T>);
