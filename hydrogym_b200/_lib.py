@@ -23,7 +23,7 @@ SYMBOLS = (
     "kf_slab_export", "kf_slab_exchange_bytes", "kf_slab_col", "kf_slab_row", "kf_slab_obs",
     "kf_slab_launch_count", "kf_slab_workspace_bytes", "kf_energy_spectrum",
     "kf_slab_p2p_init", "kf_slab_p2p_attach", "kf_slab_p2p_attach_local", "kf_physical_fields",
-    "kf_slab_barrier", "kf_slab_rk_steps",
+    "kf_slab_barrier", "kf_slab_rk_steps", "kf_reward_obs_noalloc",
     "kf_set_control_field", "kf_nonlinear_terms", "kf_linear_terms", "kf_implicit_timestep", "kf_strain_diagnostics",
 )
 
@@ -61,6 +61,8 @@ def load():
     lib.kf_rollout.argtypes = [vp, vp, vp, vp, vp]
     lib.kf_rk_steps.argtypes = [vp, vp, vp, ctypes.c_int, vp]
     lib.kf_reward_obs.argtypes = [vp, vp, ctypes.c_int, vp, vp, vp, vp]
+    lib.kf_reward_obs_noalloc.argtypes = [vp, vp, ctypes.c_int, vp, vp, vp, vp]
+    lib.kf_reward_obs_noalloc.restype = ctypes.c_int
     lib.kf_step.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
     lib.kf_step_host.argtypes = [vp, vp, vp, vp, vp, vp]
     fp = ctypes.POINTER(ctypes.c_float)

@@ -1088,3 +1088,74 @@ int kf_nonlinear_terms(kf_handle h, const void* omega_hat_dev, const void* actio
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of kf_reward_obs (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops, harnesses that forbid
+// it).  kf_reward_obs keeps its per-(environment, snapshot) partial sums -- 4 doubles each -- in a buffer it
+// cudaMallocs on first use and grows on demand (ensure_acc); here that scratch is a file-scope device array of a
+// fixed, modest size that every GPU loading the library holds until exit.
+// ---------------------------------------------------------------------------------------------------------------
+// KF_NOALLOC_MAX_ENV_SNAPSHOTS (include/kolmo_b200.h) = 16384: B * n_snap <= this; the array is 16384 * 4 * 8 B = 512 KiB per GPU
+
+static __device__ __align__(256) double g_noalloc_acc[4 * KF_NOALLOC_MAX_ENV_SNAPSHOTS];
+
+namespace {
+
+// Device address of g_noalloc_acc on `device` (which must be current).  In HOST code the array's name is only a
+// host-side stand-in for the symbol, not a device address: the kernels must be given what cudaGetSymbolAddress
+// returns, looked up once per device.
+int noalloc_scratch(int device, double** out) {
+  constexpr int kMaxDevices = 64;
+  static double* table[kMaxDevices] = {};
+  if (device < 0 || device >= kMaxDevices) return fail("kf_reward_obs_noalloc: device ordinal out of range");
+  if (!table[device]) {
+    double* p = nullptr;
+    KF_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_acc));
+    if (!p) return fail("kf_reward_obs_noalloc: cudaGetSymbolAddress returned a null address");
+    table[device] = p;
+  }
+  *out = table[device];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int kf_reward_obs_noalloc(kf_handle h, const void* trajectory_dev, int n_snap, void* obs_dev,
+                                     void* mean_tke_dev, int* nonfinite_dev, void* stream) {
+  if (!h || !trajectory_dev) return fail("kf_reward_obs_noalloc: null argument");
+  if (n_snap < 1) return fail("kf_reward_obs_noalloc: n_snap must be >= 1");
+  Ctx& c = h->c;
+  const long long need = (long long)c.cfg.B * (long long)n_snap;
+  if (need > KF_NOALLOC_MAX_ENV_SNAPSHOTS)
+    return fail("kf_reward_obs_noalloc: B * n_snap = " + std::to_string(need) + " exceeds the static scratch of " +
+                std::to_string(KF_NOALLOC_MAX_ENV_SNAPSHOTS) + " environment-snapshots (use kf_reward_obs)");
+  DeviceGuard guard(c.cfg.device);
+  double* acc = nullptr;
+  if (int rc = noalloc_scratch(c.cfg.device, &acc)) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t el = c.ops->elem, real = el / 2;
+  const int B = c.cfg.B;
+  const size_t user_env = (size_t)c.N * (c.MH + 1);
+  const int nobs2 = c.cfg.obs_size * c.cfg.obs_size;
+  // the array keeps the previous call's sums: the part this call accumulates into must start at zero
+  KF_CUDA(cudaMemsetAsync(acc, 0, sizeof(double) * 4 * (size_t)B * n_snap, s));
+  if (obs_dev) KF_CUDA(cudaMemsetAsync(obs_dev, 0, real * (size_t)B * nobs2, s));
+  for (int b0 = 0; b0 < B; b0 += c.chunk) {
+    const int nb = (B - b0 < c.chunk) ? (B - b0) : c.chunk;
+    for (int j = 0; j < n_snap; ++j) {
+      const char* tj = (const char*)trajectory_dev + el * user_env * ((size_t)b0 * n_snap + j);
+      c.ops->import_(c, nb, tj, user_env * n_snap, s);
+      c.ops->col(c, nb, stage_of(c, 0), kf::kColInit, s);  // fields of the snapshot -> x-space
+      c.ops->obs(c, nb, acc + 4 * ((size_t)b0 * n_snap + j), 4 * (size_t)n_snap,
+                 obs_dev ? (char*)obs_dev + real * (size_t)b0 * nobs2 : nullptr, 1.0 / n_snap, s);
+      c.launches += 3;
+    }
+  }
+  Ctx view = c;  // shallow copy (owns nothing): the finalize kernel reads its sums through Ctx::acc
+  view.acc = acc;
+  c.ops->finalize(view, n_snap, mean_tke_dev, nonfinite_dev, s);
+  c.launches += 1;
+  KF_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -72,6 +72,19 @@ int kf_rk_steps(kf_handle h, void* omega_hat_dev, const void* actions_dev, int n
 int kf_reward_obs(kf_handle h, const void* trajectory_dev, int n_snap, void* obs_dev, void* mean_tke_dev,
                   int* nonfinite_dev, void* stream);
 
+/* kf_reward_obs without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments, same results as kf_reward_obs; the per-(environment, snapshot) partial sums live in a static
+ * device array inside the library instead of a buffer that kf_reward_obs cudaMallocs and grows on demand.
+ * Limit: B * n_snap <= KF_NOALLOC_MAX_ENV_SNAPSHOTS (16384; the array is 512 KiB, held by every GPU that loads the
+ * library until the process exits); larger requests fail with a message (use kf_reward_obs).  The call itself calls no
+ * cudaMalloc / cudaFree / allocating routine (the handle's workspace was allocated by kf_create).  ALL calls on a
+ * device share the one array: it is cleared at the start of each call, and two calls that overlap on the GPU (different
+ * streams or handles) race -- serialise them. */
+#define KF_NOALLOC_MAX_ENV_SNAPSHOTS 16384
+int kf_reward_obs_noalloc(kf_handle h, const void* trajectory_dev, int n_snap, void* obs_dev, void* mean_tke_dev,
+                          int* nonfinite_dev, void* stream);
+
 /* Physical-space fields of omega_hat_dev [B][N][M/2+1] (irfftn of the spectral fields of compute_velocity_fft
  * utils.py:53-69 and of the two vorticity gradients kolmogorov.py:240-247): out_dev [nfields][B][N][M] real,
  * fields in the order u, v, d(omega)/dx, d(omega)/dy (nfields = 1..4).  Scratches the workspace. */
