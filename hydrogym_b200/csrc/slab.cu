@@ -34,6 +34,7 @@ struct SlabCtx;
 
 struct SlabOps {
   size_t elem;  // bytes per complex
+  int col_groups;  // columns per CTA of the ordinary column kernel
   cudaError_t (*prepare)();
   void (*fill_tw)(double* re_im);  // transposed twiddle table of the plan (fft.cuh), N complex
   void (*fill_tw2)(double* re_im);  // the same for the length-N/2 plan of the row kernel, N/2 complex
@@ -65,6 +66,14 @@ struct SlabCtx {
   // the one-CTA kernel of the packed column runs beside the main column kernel on its own stream
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // peer-to-peer mode, P > 1, KF_SLAB_COL_CHUNKS = n > 1 (experiment, off by default): the column pass runs in n
+  // pieces; the field transposes of piece i (remote stores over NVLink) run on `side2` while the column kernel of piece
+  // i + 1 runs on the main stream.  Measured ms per RK step at 8192^2 fp32 with 1 / 2 / 4 pieces: 6.28 / 6.59 / 6.62
+  // on 2 GPUs, 2.33 / 2.35 / 2.87 on 8 GPUs -- the transposes' blocks crowd out the 1024-thread column CTAs.
+  static constexpr int kMaxColChunks = 8;
+  int col_chunks = 1;
+  cudaStream_t side2 = nullptr;
+  cudaEvent_t ev_chunk[kMaxColChunks] = {}, ev_side2 = nullptr;
   // device-side cross-rank barrier (peer-to-peer mode, one process per GPU): flag words behind own_adv
   // ([0..P) = arrival epochs written by the peers, [KF_MAX_PEERS] = this rank's epoch counter)
   unsigned* flags = nullptr;
@@ -103,6 +112,12 @@ __global__ void slab_barrier_kernel(BarrierArgs a) {
     } while ((int)(v - e) < 0);
   }
   __syncthreads();
+}
+
+// pieces the column pass is cut into (see SlabImpl::col): > 1 only with remote stores to several GPUs
+int col_pieces(const SlabCtx& c, bool remote_stores) {
+  const int ncb = c.Q / c.ops->col_groups;
+  return (remote_stores && c.P > 1 && c.side2 && c.col_chunks > 1 && ncb % c.col_chunks == 0) ? c.col_chunks : 1;
 }
 
 template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS, int CMINB = 2, int TWS = 0, bool LEAN = false>
@@ -150,6 +165,7 @@ struct SlabImpl {
     a.q0 = c.rank * c.Q; a.x0 = c.rank * c.X;
     a.Q = c.Q; a.X = c.X; a.lgQ = c.lgQ;
     a.row_prefetch = c.row_prefetch;
+    a.cb0 = 0; a.cb1 = c.Q / GROUPS;
     return a;
   }
 
@@ -160,17 +176,23 @@ struct SlabImpl {
     return blocks < occ * c.sms ? blocks : occ * c.sms;
   }
 
-  template <int MODE> static void col_kernels(const SlabCtx& c, const kf::SlabArgs<T>& a, cudaStream_t s) {
+  // column blocks [cb0, cb1) of the ordinary columns; first = true also runs the packed column 0 (rank 0) beside it
+  template <int MODE>
+  static void col_kernels(const SlabCtx& c, kf::SlabArgs<T> a, cudaStream_t s, int cb0, int cb1, bool first) {
     auto main_k = kf::slab_col_scalar_kernel<T, P, GROUPS, MODE, CMINB, TWS>;
     const int threads = P::TPF * GROUPS;
-    if (c.rank == 0) {
+    if (first && c.rank == 0) {
       cudaEventRecord(c.ev_fork, s);
       cudaStreamWaitEvent(c.side, c.ev_fork, 0);
       kf::slab_col_kernel<T, P, 1, MODE, true, 1, LEAN><<<1, P::TPF, smem(1), c.side>>>(a);
       cudaEventRecord(c.ev_join, c.side);
     }
-    main_k<<<wave(c, main_k, threads, smem_scalar(), c.Q / GROUPS), threads, smem_scalar(), s>>>(a);
-    if (c.rank == 0) cudaStreamWaitEvent(s, c.ev_join, 0);
+    a.cb0 = cb0; a.cb1 = cb1;
+    main_k<<<wave(c, main_k, threads, smem_scalar(), cb1 - cb0), threads, smem_scalar(), s>>>(a);
+    if (first && c.rank == 0) cudaStreamWaitEvent(s, c.ev_join, 0);
+  }
+  template <int MODE> static void col_kernels(const SlabCtx& c, const kf::SlabArgs<T>& a, cudaStream_t s) {
+    col_kernels<MODE>(c, a, s, 0, c.Q / GROUPS, true);
   }
 
   template <typename V> static void transpose(const V* in, V* out, kf::TransposeArgs p, int nz, cudaStream_t s) {
@@ -180,12 +202,29 @@ struct SlabImpl {
     while ((1 << p.out_lg) < p.out_rpb) ++p.out_lg;
     kf::transpose_kernel<V><<<grid, 256, 0, s>>>(in, out, p);
   }
+  // the same for logical input rows [r0, r1) only
+  template <typename V>
+  static void transpose_rows(const V* in, V* out, kf::TransposeArgs p, int nz, int r0, int r1, cudaStream_t s) {
+    const dim3 grid((p.Cn + 31) / 32, (r1 - r0 + 31) / 32, nz);
+    p.in_lg = p.out_lg = 0;
+    while ((1 << p.in_lg) < p.in_rpb) ++p.in_lg;
+    while ((1 << p.out_lg) < p.out_rpb) ++p.out_lg;
+    p.r_off = r0;
+    p.R = r1;
+    kf::transpose_kernel<V><<<grid, 256, 0, s>>>(in, out, p);
+  }
 
   // stage >= 0: received advection blocks -> K layout -> sub-stage `stage` -> fields -> send blocks;
   // stage < 0: fields of the stored omega_hat only
   static void col(const SlabCtx& c, int stage, const void* adv_recv, void* fld_send, cudaStream_t s) {
     kf::SlabArgs<T> a = args(c);
     const int Q = c.Q, X = c.X;
+    // field planes [4][Q][N] -> blocks [4][X][Q] per destination rank d (rows x in [d*X, (d+1)*X), plane z at
+    // + z*XQ): block d of the local send buffer, or slot `rank` of rank d's receive buffer written over NVLink
+    kf::TransposeArgs pf{Q, N, Q, X, 0, (size_t)N, (size_t)Q * N, 4 * (size_t)X * Q, (size_t)Q, (size_t)X * Q, {}};
+    for (int d = 0; d < c.P; ++d)
+      pf.out_tab[d] = fld_send ? (void*)((C*)fld_send + (size_t)d * 4 * X * Q)
+                               : (void*)((C*)c.peer_fld[d] + (size_t)c.rank * 4 * X * Q);
     if (stage >= 0) {
       // adv_recv [P][X][Q] is [N][Q] with plain rows -> advk [Q][N]
       kf::TransposeArgs p{N, Q, N, Q, 0, (size_t)Q, 0, 0, (size_t)N, 0, {}};
@@ -193,17 +232,27 @@ struct SlabImpl {
       a.beta = (T)kBeta[stage];
       a.gdt = (T)(kGamma[stage] * c.cfg.dt);                                        // base.py:55
       a.munu = (T)(0.5 * c.cfg.dt * (kAlpha[stage + 1] - kAlpha[stage]) * c.cfg.nu);  // base.py:54
-      col_kernels<kf::kSlabStage>(c, a, s);
-    } else {
-      col_kernels<kf::kSlabInit>(c, a, s);
     }
-    // field planes [4][Q][N] -> blocks [4][X][Q] per destination rank d (rows x in [d*X, (d+1)*X), plane z at
-    // + z*XQ): block d of the local send buffer, or slot `rank` of rank d's receive buffer written over NVLink
-    kf::TransposeArgs p{Q, N, Q, X, 0, (size_t)N, (size_t)Q * N, 4 * (size_t)X * Q, (size_t)Q, (size_t)X * Q, {}};
-    for (int d = 0; d < c.P; ++d)
-      p.out_tab[d] = fld_send ? (void*)((C*)fld_send + (size_t)d * 4 * X * Q)
-                              : (void*)((C*)c.peer_fld[d] + (size_t)c.rank * 4 * X * Q);
-    transpose<C>((const C*)c.fk, (C*)nullptr, p, 4, s);
+    const int ncb = Q / GROUPS;
+    const int nch = col_pieces(c, !fld_send);
+    if (nch == 1) {
+      if (stage >= 0) col_kernels<kf::kSlabStage>(c, a, s);
+      else col_kernels<kf::kSlabInit>(c, a, s);
+      transpose<C>((const C*)c.fk, (C*)nullptr, pf, 4, s);
+      return;
+    }
+    // Peer-to-peer exchange over several GPUs: the remote stores of the field transposes are bound by NVLink, the
+    // column kernel sends nothing.  Pipeline them: piece i's transposes (stream side2) under piece i + 1's kernel.
+    const int per = ncb / nch;
+    for (int i = 0; i < nch; ++i) {
+      if (stage >= 0) col_kernels<kf::kSlabStage>(c, a, s, i * per, (i + 1) * per, i == 0);
+      else col_kernels<kf::kSlabInit>(c, a, s, i * per, (i + 1) * per, i == 0);
+      cudaEventRecord(c.ev_chunk[i], s);
+      cudaStreamWaitEvent(c.side2, c.ev_chunk[i], 0);
+      transpose_rows<C>((const C*)c.fk, (C*)nullptr, pf, 4, i * per * GROUPS, (i + 1) * per * GROUPS, c.side2);
+    }
+    cudaEventRecord(c.ev_side2, c.side2);
+    cudaStreamWaitEvent(s, c.ev_side2, 0);
   }
 
   static void row(const SlabCtx& c, const void* fld_recv, void* adv_send, cudaStream_t s) {
@@ -246,6 +295,7 @@ struct SlabImpl {
   static SlabOps make() {
     SlabOps o;
     o.elem = sizeof(C);
+    o.col_groups = GROUPS;
     o.prepare = prepare; o.fill_tw = kf::fill_twiddles<P>; o.fill_tw2 = kf::fill_twiddles<PH>; o.col = col; o.row = row; o.obs = obs;
     o.import_ = import_; o.export_ = export_; o.forcing = forcing;
     return o;
@@ -306,6 +356,10 @@ void free_all(SlabCtx& c) {
   }
   if (c.graph) cudaGraphExecDestroy(c.graph);
   if (c.side) cudaStreamDestroy(c.side);
+  if (c.side2) cudaStreamDestroy(c.side2);
+  if (c.ev_side2) cudaEventDestroy(c.ev_side2);
+  for (cudaEvent_t e : c.ev_chunk)
+    if (e) cudaEventDestroy(e);
   if (c.ev_fork) cudaEventDestroy(c.ev_fork);
   if (c.ev_join) cudaEventDestroy(c.ev_join);
   void* ptrs[] = {c.wk, c.hk, c.wnyq, c.hnyq, c.G, c.advk, c.fk, c.tw, c.tw2, c.twh, c.F, c.C, c.own_fld, c.own_adv};
@@ -375,7 +429,15 @@ int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks) {
     cudaError_t e = cudaStreamCreateWithFlags(&c.side, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c.side2, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c.ev_side2, cudaEventDisableTiming);
+    for (int i = 0; i < SlabCtx::kMaxColChunks && e == cudaSuccess; ++i)
+      e = cudaEventCreateWithFlags(&c.ev_chunk[i], cudaEventDisableTiming);
     if (e != cudaSuccess) rc = fail(std::string("side stream: ") + cudaGetErrorString(e));
+    if (const char* ev = getenv("KF_SLAB_COL_CHUNKS")) {
+      const int v = atoi(ev);
+      if (v >= 1 && v <= SlabCtx::kMaxColChunks) c.col_chunks = v;
+    }
   }
   cudaError_t pe = ops->prepare();
   if (pe != cudaSuccess) rc = fail(std::string("kernel attribute setup: ") + cudaGetErrorString(pe));
@@ -494,7 +556,7 @@ int kf_slab_col(kf_slab h, int stage, const void* adv_recv_dev, void* fld_send_d
   if (stage >= 0 && !c.have_constants) return fail("kf_slab_set_constants has not been called");
   DeviceGuard guard(c.cfg.device);
   c.ops->col(c, stage, adv_recv_dev, fld_send_dev, (cudaStream_t)stream);
-  c.launches += (stage >= 0 ? 3 : 2) + (c.rank == 0 ? 1 : 0);
+  c.launches += (stage >= 0 ? 3 : 2) + (c.rank == 0 ? 1 : 0) + 2 * (col_pieces(c, !fld_send_dev) - 1);
   KF_CUDA(cudaGetLastError());
   return 0;
 }
@@ -598,7 +660,7 @@ void enqueue_rk_step(SlabCtx& c, cudaStream_t s) {
     enqueue_barrier(c, s);  // every rank's advection blocks have landed
     c.ops->col(c, stage, nullptr, nullptr, s);
     enqueue_barrier(c, s);  // every rank's field blocks have landed
-    c.launches += 4 + (c.rank == 0 ? 1 : 0);
+    c.launches += 4 + (c.rank == 0 ? 1 : 0) + 2 * (col_pieces(c, true) - 1);
   }
 }
 
@@ -642,7 +704,7 @@ int kf_slab_rk_steps(kf_slab h, int n_steps, void* stream) {
     cudaGraphDestroy(g);
     if (ce != cudaSuccess) return fail(std::string("kf_slab_rk_steps: cudaGraphInstantiate: ") + cudaGetErrorString(ce));
   }
-  const long long per_step = 5LL * (4 + (c.rank == 0 ? 1 : 0) + (c.P > 1 ? 2 : 0));
+  const long long per_step = 5LL * (4 + (c.rank == 0 ? 1 : 0) + (c.P > 1 ? 2 : 0) + 2 * (col_pieces(c, true) - 1));
   for (int i = 0; i < n_steps; ++i) {
     if (c.graph) {
       KF_CUDA(cudaGraphLaunch(c.graph, s));

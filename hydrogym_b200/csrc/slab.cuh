@@ -51,6 +51,7 @@ template <typename T> struct SlabArgs {
   int x0;               // global x of local row 0 (rank * X)
   int Q, X, lgQ;
   int row_prefetch;     // slab_row_half_kernel: L2 bulk prefetch of the next pair of field rows (KF_SLAB_ROW_PREFETCH)
+  int cb0, cb1;         // slab_col_scalar_kernel: range of column blocks (of GROUPS columns) this launch covers
 };
 
 // split exchange of one FFT group over a padded buffer of lane values (real parts, then imaginary parts)
@@ -276,9 +277,9 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_scalar_kernel(S
     if (GROUPS > 1 && TPF > 32) ex.bar = 1 + g;
   }
 
-  const int ncb = a.Q / GROUPS;
+  const int ncb = a.cb1;
 #pragma unroll 1
-  for (int cb = blockIdx.x; cb < ncb; cb += gridDim.x) {
+  for (int cb = a.cb0 + blockIdx.x; cb < ncb; cb += gridDim.x) {
     int t = t0;
     asm volatile("" : "+r"(t));  // see slab_col_kernel
     const int ql = cb * GROUPS + g;
@@ -562,13 +563,14 @@ struct TransposeArgs {
   // out + j*out_blk: the blocks may live on different GPUs (peer-mapped receive buffers)
   void* out_tab[KF_MAX_PEERS];
   int in_lg, out_lg;  // log2 of in_rpb / out_rpb (both are powers of two; filled in by the launcher)
+  int r_off;          // first logical input row of this launch (rows r_off .. R-1; 0 = all)
 };
 
 template <typename V> __global__ void __launch_bounds__(256) transpose_kernel(const V* __restrict__ in, V* __restrict__ out,
                                                                               TransposeArgs p) {
   __shared__ V tile[32][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const int c0 = blockIdx.x * 32, r0 = p.r_off + blockIdx.y * 32;
   in += (size_t)blockIdx.z * p.in_z;
   out += (size_t)blockIdx.z * p.out_z;
 #pragma unroll

@@ -159,3 +159,25 @@ def test_solver_surface_callbacks_observations_and_npy(tmp_path):
     io.save_trajectory(str(tmp_path / "traj.npy"), traj)
     back = io.load_trajectory(str(tmp_path / "traj.npy"), device="cuda")
     assert torch.equal(back, traj)
+
+
+def test_vector_env_truncation_resets_state_obs_and_trajectory_without_reset_call():
+    """Auto-reset after ``set_state`` (no ``reset()`` before): environments that hit ``max_episode_steps`` take the
+    cached post-reset state, observation and trajectory (gymnax ``Environment.step`` semantics)."""
+    from hydrogym_b200 import KolmogorovVectorEnv
+    venv = KolmogorovVectorEnv(3, dict(ENV_CFG), FLOW_CFG, dtype="float64", device="cuda:0", keep_trajectory=True)
+    venv.params = venv.params.replace(max_episode_steps=2)
+    ref_obs, ref_state = venv.env.reset_env(None, venv.params)
+    w0 = ref_state.omega_hat.unsqueeze(0).repeat(3, 1, 1) * torch.tensor([1.0, 0.9, 1.1], device="cuda")[:, None, None]
+    venv.set_state(w0.contiguous())
+    acts = torch.zeros(3, 4, dtype=torch.float64)
+    _, _, term, trunc, _ = venv.step(acts)
+    assert not bool(trunc.any()) and not bool(term.any()) and venv.time.tolist() == [1, 1, 1]
+    obs, reward, term, trunc, info = venv.step(acts)
+    assert bool(trunc.all()) and venv.time.tolist() == [0, 0, 0]
+    for b in range(3):
+        assert torch.equal(venv.omega_hat[b], ref_state.omega_hat)
+        assert torch.equal(venv.trajectory[b], ref_state.trajectory)
+        assert torch.equal(obs[b], ref_obs)
+    assert not torch.equal(info["final_observation"][1], ref_obs)  # the step's own observation is kept in info
+    venv.close()

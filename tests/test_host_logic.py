@@ -102,3 +102,17 @@ def test_radix_butterflies_on_host():
     subprocess.check_call(["nvcc", "-std=c++17", "-O2", "-Wno-deprecated-gpu-targets", src, "-o", exe])
     out = subprocess.run([exe], capture_output=True, text=True)
     assert out.returncode == 0, out.stdout
+
+
+def test_non_default_domain_is_refused_not_silently_mixed():
+    """The kernels work on integer wavenumbers (period 2*pi): any other domain must raise instead of combining
+    host-side constants of one domain with device-side operators of another (kolmogorov.py:33-34 defaults)."""
+    import numpy as np
+    import pytest
+    from hydrogym_b200 import constants
+    from hydrogym_b200.envs.kolmogorov import FlowConfig
+    constants.check_domain((0, 2 * np.pi), (0, 2 * np.pi))
+    FlowConfig(grid_size=(64, 64))
+    for bad in (dict(domain_x=(0, 4 * np.pi)), dict(domain_y=(0, np.pi)), dict(domain_x=(1.0, 1.0 + 2 * np.pi))):
+        with pytest.raises(ValueError, match="default domain"):
+            FlowConfig(grid_size=(64, 64), **bad)
