@@ -23,6 +23,7 @@
 // Wavenumbers are the integers p = fftfreq index, q = rfftfreq index (2*pi*kx = p).
 #pragma once
 #include <cstdint>
+#include <type_traits>
 
 #include "fft.cuh"
 
@@ -65,7 +66,11 @@ __device__ __forceinline__ void stc_hint(Cx<double>* p, Cx<double> a, uint64_t p
   asm volatile("st.global.L2::cache_hint.v2.f64 [%0], {%1, %2}, %3;" ::"l"(p), "d"(a.x), "d"(a.y), "l"(pol) : "memory");
 }
 
-// exchange policy of the column kernel: TC columns interleaved, conflict-free
+// exchange policy of the column kernel: TC columns interleaved, element (pos, c) at pos * TC + c.  Reads (pos = t +
+// TPF * m) of a warp's 32 / TC consecutive t are side by side; the pass-0 scatters (pos = 16 t + r) of adjacent t are
+// 16 * TC elements apart, a 2-way conflict for 8-byte elements at TC = 8.  An XOR swizzle of the position (bit 0 with
+// bit 4) removes it within the same footprint but costs more address arithmetic than it saves: 256^2 x 256 fp32
+// 0.881 -> 0.909 ms per RK step, 512^2 1.235 -> 1.348 (profiles/r2_exchange_layout_ab.txt).  Left as it is.
 template <typename X, int TC> struct ColEx {
   static constexpr bool kSplit = false;
   Cx<X>* sm; int c;
@@ -83,14 +88,39 @@ template <typename X, int TC> struct ColExSplit {
   __device__ __forceinline__ void sync() { __syncthreads(); }
 };
 
-// exchange policy of the row kernels: one padded buffer per FFT group
+// exchange policy of the row kernels: one padded buffer per FFT group.
+// Lane-paired complex128 elements (Cx<D2>, 32 bytes) are kept as TWO PLANES of 16-byte lane pairs (x parts in
+// [0, n), y parts in [n, 2n), n = elements in the buffer) when n > 0: 128-bit shared accesses are served per
+// quarter-warp, and 8 threads on consecutive 32-byte elements hit every bank group twice (ncu on the fp64 row kernel:
+// 40 % of the shared wavefronts were conflicts, LSU pipe at 81 %); on consecutive 16-byte slots they are conflict-free,
+// and so are the pass-0 scatters (element stride 17 after padding).  Same footprint as the interleaved layout.
 template <typename X, int TPF> struct RowEx {
   static constexpr bool kSplit = false;
+  static constexpr bool kPlanar = std::is_same<X, D2>::value;
   Cx<X>* sm;
   int bar = 0;  // > 0: named barrier of this group's TPF threads (groups of one CTA run out of phase); 0: whole CTA
+  int n = 0;    // Cx<D2> only: > 0 selects the two-plane layout over n elements
   __device__ __forceinline__ static int pad(int pos) { return pos + (pos >> 4); }
-  __device__ __forceinline__ void store(int pos, Cx<X> a) { stc(sm + pad(pos), a); }
-  __device__ __forceinline__ Cx<X> load(int pos) { return ldc(sm + pad(pos)); }
+  __device__ __forceinline__ void store(int pos, Cx<X> a) {
+    if constexpr (kPlanar) {
+      if (n > 0) {
+        X* pl = reinterpret_cast<X*>(sm);
+        stl(pl + pad(pos), a.x);
+        stl(pl + n + pad(pos), a.y);
+        return;
+      }
+    }
+    stc(sm + pad(pos), a);
+  }
+  __device__ __forceinline__ Cx<X> load(int pos) {
+    if constexpr (kPlanar) {
+      if (n > 0) {
+        const X* pl = reinterpret_cast<const X*>(sm);
+        return mk<X>(ldl(pl + pad(pos)), ldl(pl + n + pad(pos)));
+      }
+    }
+    return ldc(sm + pad(pos));
+  }
   __device__ __forceinline__ void sync() {
     if (TPF <= 32) __syncwarp();
     else if (bar == 0) __syncthreads();
@@ -410,7 +440,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) row_kernel(StageArgs<T> 
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
   Cx<L2>* s_ex = reinterpret_cast<Cx<L2>*>(smem_raw) + (size_t)g * EXN;
   Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
-  RowEx<L2, TPF> ex2{s_ex};
+  RowEx<L2, TPF> ex2{s_ex, 0, EXN};
   RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_ex)};
   // the column kernel walks the environments in ascending order, so its LAST outputs are the ones
   // still in L2: start from the last environment
@@ -518,7 +548,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS) row_obs_kernel(ObsArgs<T> a) {
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
   Cx<L2>* s_ex = reinterpret_cast<Cx<L2>*>(smem_raw) + (size_t)g * EXN;
   Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
-  RowEx<L2, TPF> ex{s_ex};
+  RowEx<L2, TPF> ex{s_ex, 0, EXN};
   const int b = blockIdx.y;
   const int x = blockIdx.x * GROUPS + g;
   const size_t roff = ((size_t)b * N + x) * MH;
@@ -572,7 +602,7 @@ __global__ void __launch_bounds__(P::TPF* GROUPS) row_fields_kernel(ObsArgs<T> a
   const int g = threadIdx.x / TPF, t = threadIdx.x % TPF;
   Cx<L2>* s_ex = reinterpret_cast<Cx<L2>*>(smem_raw) + (size_t)g * EXN;
   Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
-  RowEx<L2, TPF> ex{s_ex};
+  RowEx<L2, TPF> ex{s_ex, 0, EXN};
   const int b = blockIdx.y;
   const int x = blockIdx.x * GROUPS + g;
   const size_t roff = ((size_t)b * N + x) * MH;

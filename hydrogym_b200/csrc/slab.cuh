@@ -397,7 +397,7 @@ __global__ void __launch_bounds__(PH::TPF* GROUPS, MINB) slab_row_half_kernel(Sl
   unsigned char* s_g = smem_raw + (size_t)g * EXN * sizeof(Cx<L2>);
   Cx<T>* s_tw = reinterpret_cast<Cx<T>*>(smem_raw + (size_t)GROUPS * EXN * sizeof(Cx<L2>));
   RowEx<T, TPF> ex1{reinterpret_cast<Cx<T>*>(s_g)};
-  RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g)};
+  RowEx<L2, TPF> ex2{reinterpret_cast<Cx<L2>*>(s_g), 0, (int)EXN};  // fp64: two-plane layout (kernels.cuh)
   const int Q = a.Q, lgQ = a.lgQ;
   const unsigned blk = (unsigned)a.fblk;  // element offsets of a slab fit 32 bits (N * N complex at most)
 
