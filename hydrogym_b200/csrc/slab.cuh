@@ -563,14 +563,13 @@ struct TransposeArgs {
   // out + j*out_blk: the blocks may live on different GPUs (peer-mapped receive buffers)
   void* out_tab[KF_MAX_PEERS];
   int in_lg, out_lg;  // log2 of in_rpb / out_rpb (both are powers of two; filled in by the launcher)
-  int r_off;          // first logical input row of this launch (rows r_off .. R-1; 0 = all)
 };
 
 template <typename V> __global__ void __launch_bounds__(256) transpose_kernel(const V* __restrict__ in, V* __restrict__ out,
                                                                               TransposeArgs p) {
   __shared__ V tile[32][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int c0 = blockIdx.x * 32, r0 = p.r_off + blockIdx.y * 32;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
   in += (size_t)blockIdx.z * p.in_z;
   out += (size_t)blockIdx.z * p.out_z;
 #pragma unroll

@@ -241,3 +241,30 @@ def test_slab_graph_replay_matches_host_loop():
         sl.close()
         assert launches > 0
     assert np.isfinite(out[True]).all() and np.array_equal(out[True], out[False])
+
+
+def test_slab_pipelined_column_pass_is_bit_identical():
+    """KF_SLAB_COL_CHUNKS = n > 1 (off by default): the column pass in n pieces with each piece's field transposes on a
+    side stream -- same kernels on the same data, so the result must not change by a bit (4 emulated ranks, p2p)."""
+    import os
+    N, steps = 256, 3
+    ref = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=np.float32)
+    w0 = torch.from_numpy(random_states(ref, 1, seed=12).astype(np.complex64)[0]).cuda()
+    act = torch.tensor(ACTION, dtype=torch.float32, device="cuda")
+    out = {}
+    old = os.environ.get("KF_SLAB_COL_CHUNKS")
+    try:
+        for pieces in ("1", "2", "4"):
+            os.environ["KF_SLAB_COL_CHUNKS"] = pieces
+            sl = make_slab(N, 100, torch.float32, 4, exchange="p2p")
+            sl.set_state(w0, act)
+            sl.rk_steps(steps)
+            out[pieces] = sl.get_state().cpu().numpy()
+            sl.close()
+    finally:
+        if old is None:
+            os.environ.pop("KF_SLAB_COL_CHUNKS", None)
+        else:
+            os.environ["KF_SLAB_COL_CHUNKS"] = old
+    assert np.isfinite(out["1"]).all()
+    assert np.array_equal(out["1"], out["2"]) and np.array_equal(out["1"], out["4"])
