@@ -307,6 +307,7 @@ const SlabOps* find_slab_ops(int dtype, int N) {
   //  [, column-kernel min CTAs per SM, twiddles of the column kernel in shared memory + per-group named barriers]>
   static const SlabOps f256 = SlabImpl<float, Plan<256, 16, 16, 16>, 8, 8, Plan<128, 8, 16, 8>, 16>::make();
   static const SlabOps f1024 = SlabImpl<float, Plan<1024, 64, 16, 4, 16>, 2, 2, Plan<512, 32, 8, 8, 8>, 4>::make();
+  static const SlabOps f2048 = SlabImpl<float, Plan<2048, 128, 16, 8, 16>, 1, 1, Plan<1024, 64, 16, 4, 16>, 2>::make();
   static const SlabOps f4096 = SlabImpl<float, Plan<4096, 256, 16, 16, 16>, 1, 1, Plan<2048, 128, 16, 8, 16>, 1>::make();
 #ifdef KF_SLAB_ROW_E8
   static const SlabOps f8192 =
@@ -324,6 +325,7 @@ const SlabOps* find_slab_ops(int dtype, int N) {
 #endif
   static const SlabOps d256 = SlabImpl<double, Plan<256, 16, 16, 16>, 8, 8, Plan<128, 8, 16, 8>, 16>::make();
   static const SlabOps d1024 = SlabImpl<double, Plan<1024, 64, 16, 4, 16>, 2, 2, Plan<512, 32, 8, 8, 8>, 4>::make();
+  static const SlabOps d2048 = SlabImpl<double, Plan<2048, 128, 16, 8, 16>, 1, 1, Plan<1024, 64, 16, 4, 16>, 2>::make();
   static const SlabOps d4096 = SlabImpl<double, Plan<4096, 256, 16, 16, 16>, 1, 1, Plan<2048, 128, 16, 8, 16>, 1>::make();
   // fp64 at 8192 points: one transform per CTA everywhere (139 KB exchange buffers), twiddles of the column kernels
   // through L1, LEAN packed-column / observation kernels
@@ -333,6 +335,7 @@ const SlabOps* find_slab_ops(int dtype, int N) {
   switch (N) {
     case 256: return f ? &f256 : &d256;
     case 1024: return f ? &f1024 : &d1024;
+    case 2048: return f ? &f2048 : &d2048;
     case 4096: return f ? &f4096 : &d4096;
     case 8192: return f ? &f8192 : &d8192;
     default: return nullptr;
@@ -393,7 +396,7 @@ int kf_slab_create(kf_slab* out, const kf_config* cfg, int rank, int nranks) {
   if (cfg->N != cfg->M) return fail("kf_slab_create: only square grids are supported (N == M)");
   if (cfg->dtype != KF_F32 && cfg->dtype != KF_F64) return fail("kf_slab_create: dtype must be KF_F32 or KF_F64");
   const SlabOps* ops = find_slab_ops(cfg->dtype, cfg->N);
-  if (!ops) return fail("kf_slab_create: grid size must be 256, 1024, 4096 or 8192");
+  if (!ops) return fail("kf_slab_create: grid size must be 256, 1024, 2048, 4096 or 8192");
   if (nranks < 1 || (nranks & (nranks - 1)) != 0) return fail("kf_slab_create: nranks must be a power of two");
   if (rank < 0 || rank >= nranks) return fail("kf_slab_create: rank out of range");
   if (cfg->N / 2 / nranks < 8) return fail("kf_slab_create: need at least 8 packed columns per rank");

@@ -48,6 +48,19 @@ class KolmogorovStepper:
         self.dt, self.nu = float(dt), 1.0 / Re
 
         self._lib = _lib.load()
+        self._large = None
+        if N > 1024:
+            # Grids beyond the batched kernels' plans (2048^2, 4096^2, 8192^2): the single-grid slab kernels on ONE rank
+            # (csrc/slab.cu: transposed K layout, one transform per CTA), environment by environment.
+            if N not in (2048, 4096, 8192):
+                raise ValueError("grid size must be a power of two between 64 and 8192")
+            from .slab import SlabKolmogorovSolver
+            self._large = SlabKolmogorovSolver(
+                grid_size=(N, M), Re=Re, k=k, control_ks=control_ks, dt=dt, dtype=dtype, device=self.device,
+                dealias=dealias, obs_size=obs_size, min_action=min_action, max_action=max_action, domain_y=domain_y,
+                local_ranks=1, exchange="p2p")
+            self._h = ctypes.c_void_p(0)
+            return
         cfg = _lib.KfConfig(N=N, M=M, B=self.B, dtype=_lib.KF_F32 if dtype == torch.float32 else _lib.KF_F64,
                             nu=self.nu, dt=self.dt, n_inner=self.n_inner, n_outer=self.n_outer,
                             dealias=int(bool(dealias)), drag=0.0, device=dev_index, obs_size=self.obs_size,
@@ -64,6 +77,7 @@ class KolmogorovStepper:
 
     def set_control_rows(self, rows):
         """Replace the 4 control basis rows (row kx=0 of control_term for unit actions)."""
+        self._unsupported_large("set_control_rows")
         np_c = np.complex64 if self.dtype == torch.float32 else np.complex128
         self.control_rows = np.ascontiguousarray(np.asarray(rows).astype(np_c))
         _lib.check(self._lib.kf_set_constants(self._h, self.forcing_row.ctypes.data_as(ctypes.c_void_p),
@@ -72,6 +86,9 @@ class KolmogorovStepper:
     def set_control_field(self, control_hat):
         """Dense control spectrum (N, Mh) -- ``control_term`` of an arbitrary ``(cfx, cfy)`` field (K:259-272) --
         added to the nonlinear term of every environment in every sub-stage; ``None`` removes it."""
+        if control_hat is None and self._large:
+            return
+        self._unsupported_large("a dense control field")
         if control_hat is None:
             _lib.check(self._lib.kf_set_control_field(self._h, ctypes.c_void_p(0)), "kf_set_control_field")
             return
@@ -85,6 +102,9 @@ class KolmogorovStepper:
 
     # -- helpers -------------------------------------------------------------
     def close(self):
+        if getattr(self, "_large", None) is not None:
+            self._large.close()
+            self._large = None
         if getattr(self, "_h", None) is not None and self._h.value:
             self._lib.kf_destroy(self._h)
             self._h = ctypes.c_void_p(0)
@@ -115,25 +135,55 @@ class KolmogorovStepper:
 
     @property
     def launch_count(self):
-        return int(self._lib.kf_launch_count(self._h))
+        return self._large.launch_count if self._large else int(self._lib.kf_launch_count(self._h))
 
     @property
     def workspace_bytes(self):
-        return int(self._lib.kf_workspace_bytes(self._h))
+        return self._large.workspace_bytes if self._large else int(self._lib.kf_workspace_bytes(self._h))
 
     @property
     def chunk(self):
-        return int(self._lib.kf_chunk(self._h))
+        return 1 if self._large else int(self._lib.kf_chunk(self._h))
 
     @property
     def lanes(self):
-        return int(self._lib.kf_lanes(self._h))
+        return 1 if self._large else int(self._lib.kf_lanes(self._h))
+
+    # -- large grids: one environment at a time through the slab kernels -------------------------------------------
+    def _large_advance(self, omega_hat, actions, n_outer, n_inner, traj, obs, tke, nonf):
+        """In place on ``omega_hat``; fills whichever of traj / obs / tke / nonf is given."""
+        sl = self._large
+        for b in range(self.B):
+            sl.set_state(omega_hat[b], None if actions is None else actions[b])
+            ob = torch.zeros(self.obs_size ** 2, dtype=self.dtype, device=self.device) if obs is not None else None
+            tk = torch.zeros((), dtype=torch.float64, device=self.device)
+            for j in range(n_outer):
+                sl.rk_steps(n_inner)
+                if traj is not None:
+                    traj[b, j] = sl.get_state()
+                if obs is not None or tke is not None:
+                    _, t = sl.reward_obs(1.0 / n_outer, obs_out=ob)
+                    tk += t / n_outer
+            omega_hat[b] = sl.get_state()
+            if obs is not None:
+                obs[b] = ob
+            if tke is not None:
+                tke[b] = tk.to(self.dtype)
+            if nonf is not None:
+                nonf[b] = (~torch.isfinite(tk)).to(torch.int32)
+
+    def _unsupported_large(self, what):
+        if self._large:
+            raise NotImplementedError(f"{what} is available for grids up to 1024^2 only")
 
     # -- device entry points ---------------------------------------------------
     def rk_steps(self, omega_hat, actions, n_steps):
         """Advance ``omega_hat`` (B, N, Mh) IN PLACE by ``n_steps`` RK solver steps."""
         self._check_state(omega_hat)
         actions = self._check_actions(actions)
+        if self._large:
+            self._large_advance(omega_hat, actions, 1, int(n_steps), None, None, None, None)
+            return omega_hat
         with torch.cuda.device(self.device):
             _lib.check(self._lib.kf_rk_steps(self._h, _ptr(omega_hat), _ptr(actions), int(n_steps), self._stream()),
                        "kf_rk_steps")
@@ -146,6 +196,9 @@ class KolmogorovStepper:
         final = omega_hat.clone()
         traj = (torch.empty((self.B, self.n_outer, self.N, self.Mh), dtype=self.cdtype, device=self.device)
                 if want_trajectory else None)
+        if self._large:
+            self._large_advance(final, actions, self.n_outer, self.n_inner, traj, None, None, None)
+            return final, traj
         with torch.cuda.device(self.device):
             _lib.check(self._lib.kf_rollout(self._h, _ptr(final), _ptr(actions), _ptr(traj), self._stream()),
                        "kf_rollout")
@@ -159,6 +212,18 @@ class KolmogorovStepper:
         obs = torch.empty((self.B, self.obs_size ** 2), dtype=self.dtype, device=self.device)
         tke = torch.empty((self.B,), dtype=self.dtype, device=self.device)
         nonf = torch.empty((self.B,), dtype=torch.int32, device=self.device)
+        if self._large:
+            T = int(trajectory.shape[1])
+            obs.zero_()
+            for b in range(self.B):
+                tk = torch.zeros((), dtype=torch.float64, device=self.device)
+                for j in range(T):
+                    self._large.set_state(trajectory[b, j], None)
+                    _, t = self._large.reward_obs(1.0 / T, obs_out=obs[b])
+                    tk += t / T
+                tke[b] = tk.to(self.dtype)
+                nonf[b] = (~torch.isfinite(tk)).to(torch.int32)
+            return obs, tke, nonf
         with torch.cuda.device(self.device):
             _lib.check(self._lib.kf_reward_obs(self._h, _ptr(trajectory), int(trajectory.shape[1]), _ptr(obs),
                                                _ptr(tke), _ptr(nonf), self._stream()), "kf_reward_obs")
@@ -174,6 +239,9 @@ class KolmogorovStepper:
         obs = torch.empty((self.B, self.obs_size ** 2), dtype=self.dtype, device=self.device)
         tke = torch.empty((self.B,), dtype=self.dtype, device=self.device)
         nonf = torch.empty((self.B,), dtype=torch.int32, device=self.device)
+        if self._large:
+            self._large_advance(final, actions, self.n_outer, self.n_inner, traj, obs, tke, nonf)
+            return final, traj, obs, tke, nonf
         with torch.cuda.device(self.device):
             _lib.check(self._lib.kf_step(self._h, _ptr(final), _ptr(actions), _ptr(traj), _ptr(obs), _ptr(tke),
                                          _ptr(nonf), self._stream()), "kf_step")
@@ -182,6 +250,7 @@ class KolmogorovStepper:
     def physical_fields(self, omega_hat, nfields=2):
         """(nfields, B, N, N) real: u, v[, d(omega)/dx, d(omega)/dy] in physical space (irfftn of the spectral
         fields of utils.py:53-69 / kolmogorov.py:240-247)."""
+        self._unsupported_large("physical_fields")
         self._check_state(omega_hat)
         out = torch.empty((int(nfields), self.B, self.N, self.M), dtype=self.dtype, device=self.device)
         with torch.cuda.device(self.device):
@@ -192,6 +261,7 @@ class KolmogorovStepper:
     def nonlinear_terms(self, omega_hat, actions=None):
         """``PseudoSpectralNavierStokes2D.nonlinear_terms`` (K:222-257) of (B, N, Mh): advection + forcing + control
         (``actions`` (B, 4) through the control rows, plus the dense field of ``set_control_field`` if set)."""
+        self._unsupported_large("nonlinear_terms")
         self._check_state(omega_hat)
         actions = self._check_actions(actions)
         out = torch.empty_like(omega_hat)
@@ -202,6 +272,7 @@ class KolmogorovStepper:
 
     def profile_kernels(self, reps=20):
         """(ms per column-kernel launch, ms per row-kernel launch) on scratch workspace data."""
+        self._unsupported_large("profile_kernels")
         a, b = ctypes.c_float(0), ctypes.c_float(0)
         with torch.cuda.device(self.device):
             _lib.check(self._lib.kf_profile_kernels(self._h, int(reps), ctypes.byref(a), ctypes.byref(b),
@@ -210,6 +281,7 @@ class KolmogorovStepper:
 
     def step_host(self, omega_hat_host, actions_host, obs_host, tke_host, nonf_host):
         """``kf_step_host``: all arguments are HOST tensors (pinned for speed); synchronous, in place."""
+        self._unsupported_large("step_host")
         _lib.check(self._lib.kf_step_host(self._h, _ptr(omega_hat_host), _ptr(actions_host), _ptr(obs_host),
                                           _ptr(tke_host), _ptr(nonf_host)), "kf_step_host")
 

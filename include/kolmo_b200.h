@@ -161,8 +161,8 @@ int kf_energy_spectrum(int dtype, int N, int B, const void* omega_hat_dev, doubl
  * buffer goes to rank d, block s of a recv buffer comes from rank s).  Exchange buffers are caller-owned
  * device memory of kf_slab_exchange_bytes(h, 0) (fields) / (h, 1) (advection) bytes each.  With P = 1 the
  * all-to-all is the identity (send and recv may be the same buffer).
- * cfg->B, n_inner, n_outer, chunk and use_graph are ignored.  Grid sizes: 256, 1024, 4096 (fp32, fp64),
- * 8192 (fp32).
+ * cfg->B, n_inner, n_outer, chunk and use_graph are ignored.  Grid sizes: 256, 1024, 2048, 4096, 8192
+ * (fp32 and fp64).
  */
 typedef struct kf_slab_s* kf_slab;
 

@@ -119,3 +119,31 @@ def test_reward_obs_match_oracle(N, dtype, tol):
     assert np.abs(obs.cpu().numpy() - want_obs).max() < tol * np.abs(want_obs).max()
     assert np.abs(tke.cpu().numpy() - want_tke).max() < tol * np.abs(want_tke).max()
     assert int(nonf.sum()) == 0
+
+
+def test_grid_beyond_1024_runs_on_the_slab_kernels_and_matches_oracle():
+    """2048^2 (and 4096^2, 8192^2) have no batched plans: KolmogorovStepper serves them environment by environment
+    through the single-grid slab kernels on one rank.  One RK step + reward / observation against the oracle."""
+    N, B = 2048, 2
+    ref = orc.KolmogorovFlow(dict(dt=2e-4), dict(Re=1000, grid_size=(N, N)), dtype=np.float32)
+    w0 = random_states(ref, B, seed=77).astype(np.complex64)
+    actions = np.array([[0.3, -0.2, 0.1, -0.4], [0.9, 0.0, -0.9, 0.2]], dtype=np.float32)  # second one gets clipped
+    clipped = ref._clip_action(actions, ref.default_params)
+    ch = ref.equation.control_term(w0, ref._control_field(clipped, ref.default_params))
+    want = ref.integrator.rk_steps(w0.copy(), 1, ch)
+    st = make_stepper(N, 1000, B, torch.float32, dt=2e-4, n_inner=1, n_outer=1)
+    assert st.lanes == 1 and st.chunk == 1
+    final, traj, obs, tke, nonf = st.step(torch.from_numpy(w0).cuda(), torch.from_numpy(actions).cuda())
+    got = final.cpu().numpy()
+    for b in range(B):
+        assert rel_l2(got[b], want[b]) < 2e-5, (b, rel_l2(got[b], want[b]))
+    assert torch.equal(traj[:, 0], final) and (nonf == 0).all()
+    want_obs = ref._trajectory_mean_obs(want[:, None])
+    want_tke = ref._avg_tke(want[:, None])
+    assert np.abs(obs.cpu().numpy() - want_obs).max() < 1e-4 * max(1.0, np.abs(want_obs).max())
+    assert np.abs(tke.cpu().numpy() / want_tke - 1).max() < 1e-4
+    with pytest.raises(NotImplementedError):
+        st.physical_fields(final)
+    st.close()
+    with pytest.raises(ValueError):
+        make_stepper(3072, 1000, 1, torch.float32)
