@@ -72,6 +72,10 @@ struct SlabCtx {
   // on 2 GPUs, 2.33 / 2.35 / 2.87 on 8 GPUs -- the transposes' blocks crowd out the 1024-thread column CTAs.
   static constexpr int kMaxColChunks = 8;
   int col_chunks = 1;
+  // peer-to-peer mode with more than one rank (KF_SLAB_DIRECT=0/1 overrides): column kernels store field columns straight into the peers' buffers, the
+  // receiver transposes them locally into fx_local before its row / observation kernels (see SlabArgs::direct)
+  bool direct = false;
+  void* fx_local = nullptr;
   cudaStream_t side2 = nullptr;
   cudaEvent_t ev_chunk[kMaxColChunks] = {}, ev_side2 = nullptr;
   // device-side cross-rank barrier (peer-to-peer mode, one process per GPU): flag words behind own_adv
@@ -117,7 +121,7 @@ __global__ void slab_barrier_kernel(BarrierArgs a) {
 // pieces the column pass is cut into (see SlabImpl::col): > 1 only with remote stores to several GPUs
 int col_pieces(const SlabCtx& c, bool remote_stores) {
   const int ncb = c.Q / c.ops->col_groups;
-  return (remote_stores && c.P > 1 && c.side2 && c.col_chunks > 1 && ncb % c.col_chunks == 0) ? c.col_chunks : 1;
+  return (remote_stores && !c.direct && c.P > 1 && c.side2 && c.col_chunks > 1 && ncb % c.col_chunks == 0) ? c.col_chunks : 1;
 }
 
 template <typename T, class P, int GROUPS, int RGROUPS, class PH, int HGROUPS, int CMINB = 2, int TWS = 0, bool LEAN = false>
@@ -166,6 +170,9 @@ struct SlabImpl {
     a.Q = c.Q; a.X = c.X; a.lgQ = c.lgQ;
     a.row_prefetch = c.row_prefetch;
     a.cb0 = 0; a.cb1 = c.Q / GROUPS;
+    a.direct = 0; a.lgX = 0;
+    while ((1 << a.lgX) < c.X) ++a.lgX;
+    for (int d = 0; d < KF_MAX_PEERS; ++d) a.fld_dst[d] = nullptr;
     return a;
   }
 
@@ -232,6 +239,13 @@ struct SlabImpl {
       a.gdt = (T)(kGamma[stage] * c.cfg.dt);                                        // base.py:55
       a.munu = (T)(0.5 * c.cfg.dt * (kAlpha[stage + 1] - kAlpha[stage]) * c.cfg.nu);  // base.py:54
     }
+    if (!fld_send && c.direct) {  // fields leave from the column kernels themselves; no sender-side transposes
+      a.direct = 1;
+      for (int d = 0; d < c.P; ++d) a.fld_dst[d] = (C*)c.peer_fld[d] + (size_t)c.rank * 4 * X * Q;
+      if (stage >= 0) col_kernels<kf::kSlabStage>(c, a, s);
+      else col_kernels<kf::kSlabInit>(c, a, s);
+      return;
+    }
     const int ncb = Q / GROUPS;
     const int nch = col_pieces(c, !fld_send);
     if (nch == 1) {
@@ -254,9 +268,17 @@ struct SlabImpl {
     cudaStreamWaitEvent(s, c.ev_side2, 0);
   }
 
+  // direct mode: received K-layout pieces [P][4][Q][X] -> X-layout blocks [P][4][X][Q] in fx_local
+  static const C* received_fields(const SlabCtx& c, const void* fld_recv, cudaStream_t s) {
+    if (fld_recv || !c.direct) return (const C*)(fld_recv ? fld_recv : c.own_fld);
+    kf::TransposeArgs p{c.Q, c.X, c.Q, c.X, 0, (size_t)c.X, (size_t)c.Q * c.X, 0, (size_t)c.Q, (size_t)c.X * c.Q, {}};
+    transpose<C>((const C*)c.own_fld, (C*)c.fx_local, p, 4 * c.P, s);
+    return (const C*)c.fx_local;
+  }
+
   static void row(const SlabCtx& c, const void* fld_recv, void* adv_send, cudaStream_t s) {
     kf::SlabArgs<T> a = args(c);
-    a.fx = (const C*)(fld_recv ? fld_recv : c.own_fld);
+    a.fx = received_fields(c, fld_recv, s);
     for (int d = 0; d < c.P; ++d)
       a.adv_dst[d] = adv_send ? (C*)adv_send + (size_t)d * c.X * c.Q : (C*)c.peer_adv[d] + (size_t)c.rank * c.X * c.Q;
     auto k = kf::slab_row_half_kernel<T, PH, HGROUPS, 2>;
@@ -267,7 +289,7 @@ struct SlabImpl {
 
   static void obs(const SlabCtx& c, const void* fld_recv, double* acc, void* obs_dev, double obs_w, cudaStream_t s) {
     kf::SlabArgs<T> a = args(c);
-    a.fx = (const C*)(fld_recv ? fld_recv : c.own_fld);
+    a.fx = received_fields(c, fld_recv, s);
     const int st = N / c.cfg.obs_size;
     kf::slab_row_obs_kernel<T, P, RGROUPS, LEAN><<<c.X / RGROUPS, P::TPF * RGROUPS, smem_obs(), s>>>(
         a, acc, (T*)obs_dev, c.cfg.obs_size, st, st, (T)obs_w);
@@ -364,7 +386,8 @@ void free_all(SlabCtx& c) {
     if (e) cudaEventDestroy(e);
   if (c.ev_fork) cudaEventDestroy(c.ev_fork);
   if (c.ev_join) cudaEventDestroy(c.ev_join);
-  void* ptrs[] = {c.wk, c.hk, c.wnyq, c.hnyq, c.G, c.advk, c.fk, c.tw, c.tw2, c.twh, c.F, c.C, c.own_fld, c.own_adv};
+  void* ptrs[] = {c.wk, c.hk, c.wnyq, c.hnyq, c.G, c.advk, c.fk, c.tw, c.tw2, c.twh, c.F, c.C, c.own_fld, c.own_adv,
+                  c.fx_local};
   for (void* p : ptrs)
     if (p) cudaFree(p);
 }
@@ -558,7 +581,8 @@ int kf_slab_col(kf_slab h, int stage, const void* adv_recv_dev, void* fld_send_d
   if (stage >= 0 && !c.have_constants) return fail("kf_slab_set_constants has not been called");
   DeviceGuard guard(c.cfg.device);
   c.ops->col(c, stage, adv_recv_dev, fld_send_dev, (cudaStream_t)stream);
-  c.launches += (stage >= 0 ? 3 : 2) + (c.rank == 0 ? 1 : 0) + 2 * (col_pieces(c, !fld_send_dev) - 1);
+  c.launches += (stage >= 0 ? 3 : 2) + (c.rank == 0 ? 1 : 0) + 2 * (col_pieces(c, !fld_send_dev) - 1) -
+                ((!fld_send_dev && c.direct) ? 1 : 0);
   KF_CUDA(cudaGetLastError());
   return 0;
 }
@@ -570,7 +594,7 @@ int kf_slab_row(kf_slab h, const void* fld_recv_dev, void* adv_send_dev, void* s
   SlabCtx& c = h->c;
   DeviceGuard guard(c.cfg.device);
   c.ops->row(c, fld_recv_dev, adv_send_dev, (cudaStream_t)stream);
-  c.launches += 1;
+  c.launches += 1 + ((!fld_recv_dev && c.direct) ? 1 : 0);
   KF_CUDA(cudaGetLastError());
   return 0;
 }
@@ -580,7 +604,7 @@ int kf_slab_obs(kf_slab h, const void* fld_recv_dev, double* acc4_dev, void* obs
   SlabCtx& c = h->c;
   DeviceGuard guard(c.cfg.device);
   c.ops->obs(c, fld_recv_dev, acc4_dev, obs_dev, obs_w, (cudaStream_t)stream);
-  c.launches += 1;
+  c.launches += 1 + ((!fld_recv_dev && c.direct) ? 1 : 0);
   KF_CUDA(cudaGetLastError());
   return 0;
 }
@@ -597,6 +621,10 @@ int kf_slab_p2p_init(kf_slab h, void* ipc_handles_out) {
     if (int rc = dev_alloc(c, &c.own_fld, 4 * tile)) return rc;
     if (int rc = dev_alloc(c, &c.own_adv, tile + 4096)) return rc;  // + the barrier's flag block (zeroed)
     c.flags = (unsigned*)((char*)c.own_adv + tile);
+    c.direct = c.P > 1;  // measured at 8192^2 fp32: 2 GPUs 6.25 -> 5.27 ms per RK step; 1 rank 9.58 -> 9.80 (off there)
+    if (const char* e = getenv("KF_SLAB_DIRECT")) c.direct = atoi(e) != 0;
+    if (c.direct)
+      if (int rc = dev_alloc(c, &c.fx_local, 4 * tile)) return rc;
   }
   if (ipc_handles_out) {
     cudaIpcMemHandle_t* out = (cudaIpcMemHandle_t*)ipc_handles_out;

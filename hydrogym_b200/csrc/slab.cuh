@@ -52,7 +52,17 @@ template <typename T> struct SlabArgs {
   int Q, X, lgQ;
   int row_prefetch;     // slab_row_half_kernel: L2 bulk prefetch of the next pair of field rows (KF_SLAB_ROW_PREFETCH)
   int cb0, cb1;         // slab_col_scalar_kernel: range of column blocks (of GROUPS columns) this launch covers
+  // direct mode: the column kernels store their x-space field columns straight into the destination ranks' receive
+  // buffers (K-layout pieces [4][Q][X] in this rank's slot: runs of X contiguous elements per column), over NVLink
+  // and under their own butterflies; the receiver transposes the pieces locally.  0 = fields go to fk (sender transposes)
+  int direct, lgX;
+  Cx<T>* fld_dst[KF_MAX_PEERS];
 };
+
+// where element x of local column ql of field plane fld goes
+template <typename T, int N> __device__ __forceinline__ Cx<T>* direct_dst(const SlabArgs<T>& a, int fld, int ql, int x) {
+  return a.fld_dst[x >> a.lgX] + ((size_t)fld * a.Q + ql) * a.X + (x & (a.X - 1));
+}
 
 // split exchange of one FFT group over a padded buffer of lane values (real parts, then imaginary parts)
 template <typename X, int TPF> struct RowExSplit {
@@ -224,7 +234,13 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_kernel(SlabArgs
     fft_regs<P, +1, L2>(f, s_tw, t, ex2);
     Cx<T>* o0 = a.fk + ((size_t)(2 * pair) * a.Q + ql) * N;  // planes 2 pair (lane 0) and 2 pair + 1 (lane 1)
     Cx<T>* o1 = o0 + (size_t)a.Q * N;
-    if (live) {
+    if (live && a.direct) {
+#pragma unroll
+      for (int m = 0; m < E; ++m) {
+        stc(direct_dst<T, N>(a, 2 * pair, ql, t + TPF * m), mk<T>(f[m].x.lo(), f[m].y.lo()));
+        stc(direct_dst<T, N>(a, 2 * pair + 1, ql, t + TPF * m), mk<T>(f[m].x.hi(), f[m].y.hi()));
+      }
+    } else if (live) {
 #pragma unroll
       for (int m = 0; m < E; ++m) {
         stc(o0 + t + TPF * m, mk<T>(f[m].x.lo(), f[m].y.lo()));
@@ -364,7 +380,10 @@ __global__ void __launch_bounds__(P::TPF* GROUPS, MINB) slab_col_scalar_kernel(S
       }
       fft_regs<P, +1, T>(f, tw, t, ex);
       Cx<T>* out = a.fk + ((size_t)fld * a.Q + ql) * N;
-      if (live) {
+      if (live && a.direct) {
+#pragma unroll
+        for (int m = 0; m < E; ++m) stc(direct_dst<T, N>(a, fld, ql, t + TPF * m), f[m]);
+      } else if (live) {
 #pragma unroll
         for (int m = 0; m < E; ++m) stc(out + t + TPF * m, f[m]);
       }

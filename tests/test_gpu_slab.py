@@ -268,3 +268,38 @@ def test_slab_pipelined_column_pass_is_bit_identical():
             os.environ["KF_SLAB_COL_CHUNKS"] = old
     assert np.isfinite(out["1"]).all()
     assert np.array_equal(out["1"], out["2"]) and np.array_equal(out["1"], out["4"])
+
+
+@pytest.mark.parametrize("dtype,P,N", [(torch.float32, 1, 256), (torch.float32, 4, 256), (torch.float32, 8, 256),
+                                       (torch.float32, 2, 1024), (torch.float64, 4, 256)])
+def test_slab_direct_field_exchange_is_bit_identical(dtype, P, N):
+    """KF_SLAB_DIRECT=1 (the default with more than one rank; 0 = sender-side transposes): the column kernels store their x-space field columns straight into the destination ranks'
+    receive buffers and the receiver transposes them locally, instead of sender-side transposes with remote stores.
+    Same arithmetic on the same values -- state, reward and observation must not change by a bit."""
+    import os
+    steps = 2
+    ref = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=np.float32)
+    cdt = np.complex64 if dtype == torch.float32 else np.complex128
+    w0 = torch.from_numpy(random_states(ref, 1, seed=21).astype(cdt)[0]).cuda()
+    act = torch.tensor(ACTION, dtype=dtype, device="cuda")
+    out = {}
+    old = os.environ.get("KF_SLAB_DIRECT")
+    try:
+        for mode in ("0", "1"):
+            os.environ["KF_SLAB_DIRECT"] = mode
+            sl = make_slab(N, 100, dtype, P, exchange="p2p")
+            sl.set_state(w0, act)
+            sl.rk_steps(steps)
+            obs, r = sl.reward_obs()
+            out[mode] = (sl.get_state().cpu().numpy(), float(r), obs.cpu().numpy())
+            sl.close()
+    finally:
+        if old is None:
+            os.environ.pop("KF_SLAB_DIRECT", None)
+        else:
+            os.environ["KF_SLAB_DIRECT"] = old
+    assert np.isfinite(out["0"][0]).all()
+    assert np.array_equal(out["0"][0], out["1"][0])
+    # the reward's partial sums are atomic adds (order not fixed): last-bit differences are allowed there
+    assert abs(out["0"][1] - out["1"][1]) <= 1e-12 * abs(out["0"][1]) + (0 if dtype == torch.float64 else 1e-6)
+    assert np.array_equal(out["0"][2], out["1"][2])
