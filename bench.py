@@ -472,6 +472,11 @@ def slab_record(torch, dist, args, dev, rank, world, max_over_ranks, peak):
              "a2a_bytes_per_gpu_per_step": a2a, "nvlink_gbs_per_gpu": a2a / (ms * 1e-3) / 1e9,
              "gpu_launches_per_rank": int(sl.launch_count - l0), "finite": finite,
              "workspace_bytes_per_gpu": int(sl.workspace_bytes)}
+        if mode == "p2p":
+            # where a sub-stage goes (per-phase entry points with events between them, no graph): mean and max over ranks
+            ph = sl.phase_times(2)
+            r["phases_us_per_substage"] = {k: {"rank0": v, "max_over_ranks": max_over_ranks(v)} for k, v in ph.items()}
+            r["phases_largest"] = max(ph, key=lambda k: r["phases_us_per_substage"][k]["max_over_ranks"])
         rec["exchanges"][mode] = r
         sl.close()
     best = min(rec["exchanges"], key=lambda m: rec["exchanges"][m]["ms_per_rk_step"])

@@ -255,6 +255,37 @@ class SlabKolmogorovSolver:
                     self._all_to_all("fld")
         self.rk_steps_done += int(n_steps)
 
+    def phase_times(self, n_steps=4):
+        """Where one sub-stage's time goes on THIS rank: advances the state by ``n_steps`` RK steps through the
+        per-phase entry points (no graph) with CUDA events between them and returns the mean microseconds per
+        sub-stage of ``row`` (received-field transposes + row kernel, advection stored to the peers), ``wait_row``
+        (cross-rank barrier after it: the slowest rank's row phase + the flag round trip), ``col`` (advection
+        transpose + column kernels, fields stored to the peers) and ``wait_col``.  Peer-to-peer mode only."""
+        if not self.p2p:
+            raise ValueError("phase_times needs exchange='p2p'")
+        names = ("row", "wait_row", "col", "wait_col")
+        n = int(n_steps) * 5
+        with torch.cuda.device(self.device):
+            s = self._stream()
+            stream = torch.cuda.current_stream(self.device)
+            ev = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(n)]
+            for i in range(n):
+                stage = i % 5
+                ev[i][0].record(stream)
+                for r in self._ranks:
+                    _lib.check(self._lib.kf_slab_row(r.h, _ptr(r.fld_recv), _ptr(r.adv_send), s), "kf_slab_row")
+                ev[i][1].record(stream)
+                self._all_to_all("adv")
+                ev[i][2].record(stream)
+                for r in self._ranks:
+                    _lib.check(self._lib.kf_slab_col(r.h, stage, _ptr(r.adv_recv), _ptr(r.fld_send), s), "kf_slab_col")
+                ev[i][3].record(stream)
+                self._all_to_all("fld")
+                ev[i][4].record(stream)
+            torch.cuda.synchronize(self.device)
+        self.rk_steps_done += int(n_steps)
+        return {nm: 1e3 * sum(e[k].elapsed_time(e[k + 1]) for e in ev) / n for k, nm in enumerate(names)}
+
     def get_state(self):
         """The full state (N, Mh) complex, assembled on every rank (all-reduce of the per-rank column slabs)."""
         out = torch.zeros((self.N, self.Mh), dtype=self.cdtype, device=self.device)

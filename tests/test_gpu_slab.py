@@ -303,3 +303,24 @@ def test_slab_direct_field_exchange_is_bit_identical(dtype, P, N):
     # the reward's partial sums are atomic adds (order not fixed): last-bit differences are allowed there
     assert abs(out["0"][1] - out["1"][1]) <= 1e-12 * abs(out["0"][1]) + (0 if dtype == torch.float64 else 1e-6)
     assert np.array_equal(out["0"][2], out["1"][2])
+
+
+def test_slab_phase_times_advance_like_rk_steps():
+    """``phase_times`` (per-phase events for the bench's slab record) runs the same kernels as ``rk_steps``."""
+    N = 256
+    ref = orc.KolmogorovFlow(flow_config=dict(Re=100, grid_size=(N, N)), dtype=np.float32)
+    w0 = torch.from_numpy(random_states(ref, 1, seed=3).astype(np.complex64)[0]).cuda()
+    act = torch.tensor(ACTION, dtype=torch.float32, device="cuda")
+    out = []
+    for timed in (False, True):
+        sl = make_slab(N, 100, torch.float32, 2, exchange="p2p")
+        sl.set_state(w0, act)
+        if timed:
+            ph = sl.phase_times(2)
+            assert set(ph) == {"row", "wait_row", "col", "wait_col"} and all(v >= 0 for v in ph.values())
+            assert ph["row"] > 0 and ph["col"] > 0
+        else:
+            sl.rk_steps(2)
+        out.append(sl.get_state().cpu().numpy())
+        sl.close()
+    assert np.array_equal(out[0], out[1])

@@ -14,6 +14,7 @@ def main():
     ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p"])
     ap.add_argument("--dt", type=float, default=0.0, help="0 = CFL-safe default 0.8/N (1e-4 at 8192)")
     ap.add_argument("--dtype", default="fp32", choices=["fp32", "fp64"])
+    ap.add_argument("--phases", type=int, default=0, help="RK steps of per-phase event timing after the run (p2p)")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -42,6 +43,13 @@ def main():
     ms = torch.tensor([e0.elapsed_time(e1) / a.steps], device="cuda")
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    phases = None
+    if a.phases > 0 and a.exchange == "p2p":
+        ph = sl.phase_times(a.phases)
+        t = torch.tensor(list(ph.values()), device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        phases = {"rank0": ph, "max_over_ranks": dict(zip(ph, t.tolist()))}
     obs, tke = sl.reward_obs()
     C = N * (N // 2 + 1) * (8 if a.dtype == "fp32" else 16)
     if rank == 0:
@@ -49,7 +57,7 @@ def main():
                           "ms_per_rk_step": float(ms), "value": 1e3 / float(ms), "unit": "RK steps/s",
                           "algorithmic_GBps_per_gpu": 70 * C / world / float(ms) / 1e6,
                           "a2a_bytes_per_gpu_per_step": 5 * 5 * C // world * (world - 1) // world,
-                          "tke": float(tke), "finite": bool(torch.isfinite(obs).all()),
+                          "phases_us_per_substage": phases, "tke": float(tke), "finite": bool(torch.isfinite(obs).all()),
                           "workspace_bytes_per_gpu": sl.workspace_bytes}), flush=True)
     sl.close()
     if world > 1:
