@@ -25,6 +25,9 @@ SYMBOLS = (
     "kf_slab_p2p_init", "kf_slab_p2p_attach", "kf_slab_p2p_attach_local", "kf_physical_fields",
     "kf_slab_barrier", "kf_slab_rk_steps", "kf_reward_obs_noalloc",
     "kf_set_control_field", "kf_nonlinear_terms", "kf_linear_terms", "kf_implicit_timestep", "kf_strain_diagnostics",
+    # include/channel_b200.h
+    "kc_create", "kc_destroy", "kc_set_operators", "kc_set_state", "kc_get_state", "kc_step", "kc_to_spectral",
+    "kc_rk4_steps", "kc_rhs", "kc_get_spectral", "kc_to_physical", "kc_launch_count", "kc_workspace_bytes",
 )
 
 
@@ -36,6 +39,16 @@ class KfConfig(ctypes.Structure):
         ("drag", ctypes.c_double), ("device", ctypes.c_int), ("obs_size", ctypes.c_int),
         ("min_action", ctypes.c_double), ("max_action", ctypes.c_double),
         ("chunk", ctypes.c_int), ("use_graph", ctypes.c_int),
+    ]
+
+
+class KcConfig(ctypes.Structure):
+    """``kc_config`` of include/channel_b200.h."""
+    _fields_ = [
+        ("B", ctypes.c_int), ("dtype", ctypes.c_int), ("device", ctypes.c_int),
+        ("nu", ctypes.c_double), ("lx", ctypes.c_double), ("ly", ctypes.c_double), ("fx", ctypes.c_double),
+        ("target_bulk_u", ctypes.c_double), ("k_det", ctypes.c_int), ("wss_plane", ctypes.c_int),
+        ("jets_on", ctypes.c_int),
     ]
 
 
@@ -116,6 +129,26 @@ def load():
         getattr(lib, name).restype = ctypes.c_int
     lib.kf_energy_spectrum.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_int, vp]
     lib.kf_energy_spectrum.restype = ctypes.c_int
+    # 3-D channel flow (include/channel_b200.h)
+    dp = ctypes.POINTER(ctypes.c_double)
+    lib.kc_create.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(KcConfig)]
+    lib.kc_destroy.argtypes = [vp]
+    lib.kc_set_operators.argtypes = [vp] + [dp] * 8
+    lib.kc_set_state.argtypes = [vp, vp, vp, vp, vp]
+    lib.kc_get_state.argtypes = [vp, vp, vp, vp, vp]
+    lib.kc_step.argtypes = [vp, vp, dp, ci, cd, cd, cd, vp, vp, vp]
+    lib.kc_to_spectral.argtypes = [vp, vp]
+    lib.kc_to_physical.argtypes = [vp, vp]
+    lib.kc_rk4_steps.argtypes = [vp, vp, dp, ci, cd, cd, cd, vp]
+    lib.kc_rhs.argtypes = [vp, vp, dp, cd, cd, vp, vp]
+    lib.kc_get_spectral.argtypes = [vp, vp, vp]
+    for name in ("kc_create", "kc_destroy", "kc_set_operators", "kc_set_state", "kc_get_state", "kc_step",
+                 "kc_to_spectral", "kc_to_physical", "kc_rk4_steps", "kc_rhs", "kc_get_spectral"):
+        getattr(lib, name).restype = ctypes.c_int
+    lib.kc_launch_count.argtypes = [vp]
+    lib.kc_launch_count.restype = ctypes.c_longlong
+    lib.kc_workspace_bytes.argtypes = [vp]
+    lib.kc_workspace_bytes.restype = ctypes.c_ulonglong
     _lib = lib
     return lib
 

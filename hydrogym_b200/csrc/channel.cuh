@@ -1,0 +1,355 @@
+// 3-D channel-flow step: tile kernels.  Reference: C = hydrogym/jax/envs/channel.py,
+// S = hydrogym/jax/solvers/base.py.  See DESIGN.md §7b for the derivation; in short:
+//
+// * the state is FFT'd over (x, y) and physical in z (fastest axis, 72 points), so every operator of the reference acts
+//   on ONE axis: x-transforms on tiles (x, z) at fixed y / ky ("X tiles", rows of 72 contiguous z), y-transforms on tiles
+//   (y, z) at fixed x ("Y tiles", one contiguous 72 x 72 block), Chebyshev matrices and the per-mode pressure inverses
+//   along z inside either tile.  A CTA owns one tile of one field in shared memory; z is the batch axis of the
+//   length-72 transforms (72 = 8 x 9 Cooley-Tukey, two register-resident butterfly stages), so shared-memory accesses
+//   are conflict-free and global accesses are runs of 72 contiguous elements.
+// * wall conditions replace whole z-planes of a field (C:227-241), and an (x, y) FFT acts plane by plane, so the
+//   reference's "to physical, fix the walls, back to spectral" is a plane replacement in EITHER space; everything the
+//   reference computes from the wall-corrected field that is linear in it (the viscous term C:286-300, the whole
+//   projection C:311-372, the mass-flux shift S:166-183) is evaluated spectrally per (kx, ky) mode, with the Hermitian
+//   projection of `.real` (C:154) applied where it matters: the x- (y-) Nyquist row of an x- (y-) derivative is zero.
+// * only the advective products need physical space: per RK stage one X pass (finish the previous stage's right-hand
+//   side, RK update, inverse x-transforms of the state and of its x-derivative), one Y pass (inverse y-transforms,
+//   two real fields per complex transform, walls, z-derivative) and one Y pass for the products + forward y-transform.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace kc {
+
+constexpr int N = 72;
+constexpr int NN = N * N;
+constexpr int V = N * N * N;
+constexpr int THREADS = 648;  // 72 z-columns x 9 butterfly lanes
+constexpr int NACT = 24;
+constexpr int NAB = 37;
+
+template <typename T> struct C2 { T x, y; };
+template <typename T> __device__ __forceinline__ C2<T> mk(T a, T b) { C2<T> r; r.x = a; r.y = b; return r; }
+template <typename T> __device__ __forceinline__ C2<T> operator+(C2<T> a, C2<T> b) { return mk<T>(a.x + b.x, a.y + b.y); }
+template <typename T> __device__ __forceinline__ C2<T> operator-(C2<T> a, C2<T> b) { return mk<T>(a.x - b.x, a.y - b.y); }
+template <typename T> __device__ __forceinline__ C2<T> operator*(T s, C2<T> a) { return mk<T>(s * a.x, s * a.y); }
+template <typename T> __device__ __forceinline__ C2<T> cmul(C2<T> a, C2<T> b) { return mk<T>(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+template <typename T> __device__ __forceinline__ void cfma(C2<T>& acc, C2<T> a, C2<T> b) {
+  acc.x = fma(a.x, b.x, acc.x); acc.x = fma(-a.y, b.y, acc.x);
+  acc.y = fma(a.x, b.y, acc.y); acc.y = fma(a.y, b.x, acc.y);
+}
+template <typename T> __device__ __forceinline__ C2<T> mul_i(C2<T> a) { return mk<T>(-a.y, a.x); }  // i * a
+
+// integer wavenumber of index i (fftfreq order; index 36 is the Nyquist line -36)
+__device__ __forceinline__ int wave(int i) { return i < N / 2 ? i : i - N; }
+__device__ __forceinline__ bool kept(int i) { int p = wave(i); return (p < 0 ? -p : p) <= N / 3; }  // U:8-19
+
+// Length-72 DFT along the slow axis of a [72][72] shared-memory tile, column z, butterfly lane r (0..8).
+// 72 = 8 x 9: lane r does the 8-point DFT over n1 of x[9 n1 + r] and the twiddle W72^(r k1) (in place: it owns those 8
+// slots), then lanes 0..7 do the 9-point DFT over n2 for k1 = r.  tw[j] = exp(-2 pi i j / 72); INV conjugates.
+// Unnormalised.  Ends with a barrier.
+template <typename T, bool INV> __device__ __forceinline__ void fft72(C2<T>* t, const C2<T>* tw, int z, int r) {
+  auto w = [&](int j) { C2<T> v = tw[j]; if (INV) v.y = -v.y; return v; };
+  {
+    C2<T> a[8];
+#pragma unroll
+    for (int n1 = 0; n1 < 8; ++n1) a[n1] = t[(9 * n1 + r) * N + z];
+#pragma unroll
+    for (int k1 = 0; k1 < 8; ++k1) {
+      C2<T> s = a[0];
+#pragma unroll
+      for (int n1 = 1; n1 < 8; ++n1) cfma(s, a[n1], w(9 * ((n1 * k1) & 7)));
+      t[(r + 9 * k1) * N + z] = cmul(s, w((r * k1) % N));
+    }
+  }
+  __syncthreads();
+  C2<T> b[9];
+  if (r < 8) {
+#pragma unroll
+    for (int n2 = 0; n2 < 9; ++n2) b[n2] = t[(n2 + 9 * r) * N + z];
+  }
+  __syncthreads();
+  if (r < 8) {
+#pragma unroll
+    for (int k2 = 0; k2 < 9; ++k2) {
+      C2<T> s = b[0];
+#pragma unroll
+      for (int n2 = 1; n2 < 9; ++n2) cfma(s, b[n2], w(8 * ((n2 * k2) % 9)));
+      t[(r + 8 * k2) * N + z] = s;
+    }
+  }
+  __syncthreads();
+}
+
+// out[m] = sum_j Mt[j][i] * in[(r + 9 m)][j] for the 8 rows of lane r, column i: a 72 x 72 real matrix (stored
+// transposed) applied along the fast axis of a tile.  `get(row, j)` reads the operand.
+template <typename T, typename Get> __device__ __forceinline__ void zmat_real(const T* Mt, int i, int r, Get get, T (&out)[8]) {
+#pragma unroll
+  for (int m = 0; m < 8; ++m) out[m] = T(0);
+  for (int j = 0; j < N; ++j) {
+    const T mji = Mt[j * N + i];
+#pragma unroll
+    for (int m = 0; m < 8; ++m) out[m] = fma(mji, get(r + 9 * m, j), out[m]);
+  }
+}
+template <typename T, typename Get> __device__ __forceinline__ void zmat_cplx(const T* Mt, int i, int r, Get get, C2<T> (&out)[8]) {
+#pragma unroll
+  for (int m = 0; m < 8; ++m) out[m] = mk<T>(T(0), T(0));
+  for (int j = 0; j < N; ++j) {
+    const T mji = Mt[j * N + i];
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const C2<T> v = get(r + 9 * m, j);
+      out[m].x = fma(mji, v.x, out[m].x);
+      out[m].y = fma(mji, v.y, out[m].y);
+    }
+  }
+}
+
+template <typename T> struct Consts {
+  const C2<T>* tw;     // [72]
+  const T* kx;         // [72] C:114-118
+  const T* ky;
+  const T* dzt;        // [72][72] transposed Dz
+  const T* dzzt;
+  const T* ainv_t;     // [37*37][72][72] transposed inverses
+  const T* jets;       // [24][72*72]
+  const T* jets_dx;
+  const T* jets_dy;
+  const C2<T>* jets_hat;
+};
+
+enum XMode { kXFirst = 0, kXMid = 1, kXLast = 2, kXForward = 3 };
+
+template <typename T> struct XArgs {
+  Consts<T> c;
+  int mode, stage, B, jets_on;
+  const C2<T>* BN;   // [3][B][V] forward-y-transformed products (x, ky, z)
+  C2<T>* S0;         // base state of the RK4 step
+  C2<T>* S;          // stage state
+  C2<T>* ACC;        // k1 + 2 k2 + 2 k3
+  C2<T>* A;          // inverse-x-transformed stage state (x, ky, z)
+  C2<T>* AX;         // ... of its x-derivative
+  C2<T>* RHS;        // optional export of this stage's k
+  const C2<T>* M0hat;  // [B][72*72] fft2 of the jet pattern of each environment's action
+  const T* gain;     // [B] -gain(t) of this stage's time (C:231-239)
+  T nu, force;       // force = fx * 72 * 72 on mode (0, 0) of field 0 (C:267-275)
+  T a_dt;            // stage state = S0 + a_dt * k
+  T acc_w;           // ACC (+)= acc_w * k
+  T dt6;             // kXLast: S = S0 + dt6 * (ACC + k)
+};
+
+// grid (3 fields, 72 ky, B), THREADS threads, dynamic smem = 2 tiles + dzzt + twiddles
+template <typename T> __global__ void __launch_bounds__(THREADS, 1) x_kernel(const XArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  C2<T>* t1 = reinterpret_cast<C2<T>*>(smem_raw);
+  C2<T>* t2 = t1 + NN;
+  T* mt = reinterpret_cast<T*>(t2 + NN);
+  C2<T>* tw = reinterpret_cast<C2<T>*>(mt + NN);
+  const int f = blockIdx.x, kyi = blockIdx.y, b = blockIdx.z;
+  const int tid = threadIdx.x, z = tid % N, r = tid / N;
+  const size_t base = ((size_t)f * a.B + b) * V + (size_t)kyi * N;  // + x * NN + z
+  if (tid < N) tw[tid] = a.c.tw[tid];
+  if (a.mode == kXMid || a.mode == kXLast)
+    for (int e = tid; e < NN; e += THREADS) mt[e] = a.c.dzzt[e];
+  const bool my = kept(kyi);
+
+  if (a.mode == kXForward) {  // plain forward x-transform of BN into S0 (C:156-161)
+#pragma unroll
+    for (int m = 0; m < 8; ++m) t1[(r + 9 * m) * N + z] = a.BN[base + (size_t)(r + 9 * m) * NN + z];
+    __syncthreads();
+    fft72<T, false>(t1, tw, z, r);
+#pragma unroll
+    for (int m = 0; m < 8; ++m) a.S0[base + (size_t)(r + 9 * m) * NN + z] = t1[(r + 9 * m) * N + z];
+    return;
+  }
+
+  if (a.mode == kXFirst) {
+#pragma unroll
+    for (int m = 0; m < 8; ++m) t1[(r + 9 * m) * N + z] = a.S0[base + (size_t)(r + 9 * m) * NN + z];
+    __syncthreads();
+  } else {
+    // ---- this stage's right-hand side k = N_hat + L (C:243-309) on the tile (kx, z) of mode column ky ----
+    const C2<T>* state = a.stage == 0 ? a.S0 : a.S;
+    if (my) {
+#pragma unroll
+      for (int m = 0; m < 8; ++m) t1[(r + 9 * m) * N + z] = a.BN[base + (size_t)(r + 9 * m) * NN + z];
+    }
+#pragma unroll
+    for (int m = 0; m < 8; ++m) t2[(r + 9 * m) * N + z] = state[base + (size_t)(r + 9 * m) * NN + z];
+    __syncthreads();
+    if (my) fft72<T, false>(t1, tw, z, r);
+    // -k2 * state on the UNcorrected state (C:296-299), then the wall planes of the tile are replaced (C:227-241)
+    const T kyv = a.c.ky[kyi];
+    C2<T> lin[8];
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const int kxi = r + 9 * m;
+      const T kxv = a.c.kx[kxi];
+      const T k2 = kxv * kxv + kyv * kyv;
+      lin[m] = (-k2) * t2[kxi * N + z];
+    }
+    __syncthreads();
+    {
+      const T g = a.gain[b];
+      const bool wall = z == 0 || z == N - 1;
+      const bool jet = f == 2 && a.jets_on && z >= 1 && z <= 5;
+      if (wall || jet) {
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+          const int kxi = r + 9 * m;
+          t2[kxi * N + z] = wall ? mk<T>(T(0), T(0)) : g * a.M0hat[(size_t)b * NN + kxi * N + kyi];
+        }
+      }
+    }
+    __syncthreads();
+    C2<T> visc[8];
+    zmat_cplx<T>(mt, z, r, [&](int row, int j) { return t2[row * N + j]; }, visc);
+    __syncthreads();  // t2 is overwritten below
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const int kxi = r + 9 * m;
+      const size_t g = base + (size_t)kxi * NN + z;
+      C2<T> k = a.nu * (lin[m] + visc[m]);
+      if (my && kept(kxi)) k = k - t1[kxi * N + z];           // -fft(N) * dealias (C:279-283)
+      if (f == 0 && kxi == 0 && kyi == 0) k.x += a.force;      // + fft of the uniform body force
+      if (a.RHS) a.RHS[g] = k;
+      const C2<T> s0 = a.S0[g];
+      C2<T> nxt;
+      if (a.mode == kXLast) {
+        nxt = s0 + a.dt6 * (a.ACC[g] + k);                    // S:148-152
+      } else {
+        a.ACC[g] = a.stage == 0 ? a.acc_w * k : a.ACC[g] + a.acc_w * k;
+        nxt = s0 + a.a_dt * k;                                // S:139-146
+      }
+      a.S[g] = nxt;
+      t1[kxi * N + z] = nxt;
+    }
+    if (a.mode == kXLast) return;
+  }
+  // ---- inverse x-transforms of the stage state and of its x-derivative (C:153-154, 170-171) ----
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int kxi = r + 9 * m;
+    const T kxv = kxi == N / 2 ? T(0) : a.c.kx[kxi];   // Hermitian projection of `.real`: Nyquist row of d/dx is zero
+    t2[kxi * N + z] = kxv * mul_i(t1[kxi * N + z]);
+  }
+  __syncthreads();
+  fft72<T, true>(t1, tw, z, r);
+  fft72<T, true>(t2, tw, z, r);
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const size_t g = base + (size_t)(r + 9 * m) * NN + z;
+    a.A[g] = t1[(r + 9 * m) * N + z];
+    a.AX[g] = t2[(r + 9 * m) * N + z];
+  }
+}
+
+template <typename T> struct YArgs {
+  Consts<T> c;
+  int B, bc, jets_on, mode;   // mode 0: products (Y2) / derivatives (Y1); 1: plain
+  const C2<T>* A;
+  const C2<T>* AX;
+  T* F;                       // [3 fields][4: f, fx, fy, fz][B][V]
+  const T* M0; const T* M0dx; const T* M0dy;   // [B][72*72]
+  const T* gain;              // [B]
+  const T* phys;              // [3][B][V] (plain forward transform of the stored state)
+  T* phys_out;                // Y1 with bc == 0: write the physical field here instead of F
+  C2<T>* BN;
+};
+
+// Y1: grid (3 fields, 72 x, B).  Inverse y-transforms (two real fields per complex transform), walls, d/dz.
+template <typename T> __global__ void __launch_bounds__(THREADS, 1) y1_kernel(const YArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  C2<T>* t1 = reinterpret_cast<C2<T>*>(smem_raw);
+  C2<T>* t2 = t1 + NN;
+  T* mt = reinterpret_cast<T*>(t2 + NN);
+  C2<T>* tw = reinterpret_cast<C2<T>*>(mt + NN);
+  const int f = blockIdx.x, xi = blockIdx.y, b = blockIdx.z;
+  const int tid = threadIdx.x, z = tid % N, r = tid / N;
+  const size_t base = ((size_t)f * a.B + b) * V + (size_t)xi * NN;  // + y * N + z: one contiguous block
+  if (tid < N) tw[tid] = a.c.tw[tid];
+  if (a.bc)
+    for (int e = tid; e < NN; e += THREADS) mt[e] = a.c.dzt[e];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int kyi = r + 9 * m;
+    const C2<T> va = a.A[base + kyi * N + z];
+    if (a.bc) {
+      const C2<T> vx = a.AX[base + kyi * N + z];
+      t1[kyi * N + z] = va + mul_i(vx);               // f + i * df/dx: both real after the transform
+      const T kyv = kyi == N / 2 ? T(0) : a.c.ky[kyi];
+      t2[kyi * N + z] = kyv * mul_i(va);
+    } else {
+      t1[kyi * N + z] = va;
+    }
+  }
+  __syncthreads();
+  fft72<T, true>(t1, tw, z, r);
+  const T sc = T(1) / T(NN);
+  if (!a.bc) {  // plain `to_physical` (C:163-168)
+#pragma unroll
+    for (int m = 0; m < 8; ++m) a.phys_out[base + (r + 9 * m) * N + z] = sc * t1[(r + 9 * m) * N + z].x;
+    return;
+  }
+  fft72<T, true>(t2, tw, z, r);
+  T fv[8], fxv[8], fyv[8];
+  const T g = a.gain[b];
+  const bool wall = z == 0 || z == N - 1;
+  const bool jet = f == 2 && a.jets_on && z >= 1 && z <= 5;
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int yi = r + 9 * m;
+    const C2<T> c1 = t1[yi * N + z];
+    fv[m] = sc * c1.x; fxv[m] = sc * c1.y; fyv[m] = sc * t2[yi * N + z].x;
+    if (wall) { fv[m] = T(0); fxv[m] = T(0); fyv[m] = T(0); }
+    if (jet) {
+      const size_t q = (size_t)b * NN + xi * N + yi;
+      fv[m] = g * a.M0[q]; fxv[m] = g * a.M0dx[q]; fyv[m] = g * a.M0dy[q];
+    }
+  }
+  __syncthreads();
+  T* fr = reinterpret_cast<T*>(t1);  // wall-corrected field as a real tile for the z-derivative
+#pragma unroll
+  for (int m = 0; m < 8; ++m) fr[(r + 9 * m) * N + z] = fv[m];
+  __syncthreads();
+  T fz[8];
+  zmat_real<T>(mt, z, r, [&](int row, int j) { return fr[row * N + j]; }, fz);
+  T* out = a.F + ((size_t)f * 4 * a.B + b) * V + (size_t)xi * NN;
+  const size_t fs = (size_t)a.B * V;
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int o = (r + 9 * m) * N + z;
+    out[o] = fv[m]; out[fs + o] = fxv[m]; out[2 * fs + o] = fyv[m]; out[3 * fs + o] = fz[m];
+  }
+}
+
+// Y2: grid (3 fields, 72 x, B).  Advective product of field f (C:262-264) or the stored physical field, forward in y.
+template <typename T> __global__ void __launch_bounds__(THREADS, 1) y2_kernel(const YArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  C2<T>* t1 = reinterpret_cast<C2<T>*>(smem_raw);
+  C2<T>* tw = t1 + NN;
+  const int f = blockIdx.x, xi = blockIdx.y, b = blockIdx.z;
+  const int tid = threadIdx.x, z = tid % N, r = tid / N;
+  if (tid < N) tw[tid] = a.c.tw[tid];
+  const size_t fs = (size_t)a.B * V;
+  const size_t e0 = (size_t)b * V + (size_t)xi * NN;
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int o = (r + 9 * m) * N + z;
+    T n;
+    if (a.mode == 1) {
+      n = a.phys[(size_t)f * fs + e0 + o];
+    } else {
+      const T* d = a.F + (size_t)f * 4 * fs + e0 + o;
+      n = a.F[e0 + o] * d[fs] + a.F[4 * fs + e0 + o] * d[2 * fs] + a.F[8 * fs + e0 + o] * d[3 * fs];
+    }
+    t1[o] = mk<T>(n, T(0));
+  }
+  __syncthreads();
+  fft72<T, false>(t1, tw, z, r);
+  const size_t base = (size_t)f * fs + e0;
+#pragma unroll
+  for (int m = 0; m < 8; ++m) a.BN[base + (r + 9 * m) * N + z] = t1[(r + 9 * m) * N + z];
+}
+
+}  // namespace kc

@@ -42,6 +42,8 @@ def test_library_exports_every_declared_symbol():
     from hydrogym_b200 import _lib
     header = open(os.path.join(ROOT, "include", "kolmo_b200.h")).read()
     declared = set(re.findall(r"\b(kf_[a-z0-9_]+)\s*\(", header))
+    channel = open(os.path.join(ROOT, "include", "channel_b200.h")).read()
+    declared |= set(re.findall(r"\b(kc_[a-z0-9_]+)\s*\(", channel))
     assert declared == set(_lib.SYMBOLS)
     lib = ctypes.CDLL(_lib.LIB_PATH)
     for name in declared:
@@ -59,6 +61,29 @@ def test_config_struct_matches_header_field_order():
     for decl in re.findall(r"(?:int|double)\s+([^;]+);", body):
         names += [n.strip() for n in decl.split(",")]
     assert names == [f[0] for f in _lib.KfConfig._fields_]
+
+
+def test_channel_config_struct_matches_header_field_order():
+    from hydrogym_b200 import _lib
+    header = open(os.path.join(ROOT, "include", "channel_b200.h")).read()
+    body = header[header.index("typedef struct {"):header.index("} kc_config;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = []
+    for decl in re.findall(r"(?:int|double)\s+([^;]+);", body):
+        names += [n.strip() for n in decl.split(",")]
+    assert names == [f[0] for f in _lib.KcConfig._fields_]
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_channel_env_fails_loudly_without_gpu():
+    """No CPU fallback: without a CUDA device the channel stepper raises instead of computing elsewhere."""
+    import numpy as np
+    from hydrogym_b200 import ChannelStepper
+    with pytest.raises(RuntimeError):
+        ChannelStepper(num_envs=1, device="cuda:0")
+    with pytest.raises(RuntimeError):
+        ChannelStepper(num_envs=1, device="cpu")
+    del np
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
