@@ -26,15 +26,17 @@ template <typename T> struct PArgs {
 };
 
 // Pressure projection C:311-372 + walls + constant-mass-flux shift S:166-183, per (kx, ky) mode along z.
-// grid (37 * 37, B): the CTA of (a, b) = (|kx|, |ky|) loads the shared inverse once and applies it to the (up to 4)
-// modes (+-a, +-b); 4 x 72 threads: thread (i, slot) owns component i of one mode.
+// grid (37 * 37, ceil(B / kEnvsPerCta)): the CTA of (a, b) = (|kx|, |ky|) loads the shared inverse once and applies it
+// to the (up to 4) modes (+-a, +-b) of kEnvsPerCta environments; 4 x 72 threads: thread (i, slot) owns component i of
+// one mode.
+constexpr int kEnvsPerCta = 8;
 template <typename T> __global__ void __launch_bounds__(4 * N) project_kernel(const PArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* ainv = reinterpret_cast<T*>(smem_raw);   // [72][72] transposed
   T* dzt = ainv + NN;
   C2<T>* vec = reinterpret_cast<C2<T>*>(dzt + NN);   // [4][72] operand of the current matvec
   __shared__ double red[N];
-  const int ia = blockIdx.x / NAB, ib = blockIdx.x % NAB, b = blockIdx.y;
+  const int ia = blockIdx.x / NAB, ib = blockIdx.x % NAB;
   const int tid = threadIdx.x, i = tid % N, slot = tid / N;
   for (int e = tid; e < NN; e += 4 * N) {
     ainv[e] = a.c.ainv_t[(size_t)blockIdx.x * NN + e];
@@ -44,10 +46,13 @@ template <typename T> __global__ void __launch_bounds__(4 * N) project_kernel(co
   const bool live = !(sx && (ia == 0 || ia == N / 2)) && !(sy && (ib == 0 || ib == N / 2));
   const int kxi = sx ? N - ia : ia, kyi = sy ? N - ib : ib;
   const size_t fs = (size_t)a.B * V;
+  const int b_end = min(a.B, (int)(blockIdx.y + 1) * kEnvsPerCta);
+  for (int b = blockIdx.y * kEnvsPerCta; b < b_end; ++b) {
   const size_t g = (size_t)b * V + ((size_t)kxi * N + kyi) * N + i;
   C2<T> u = mk<T>(0, 0), v = u, w = u;
   if (live) { u = a.S[g]; v = a.S[fs + g]; w = a.S[2 * fs + g]; }
   C2<T>* my = vec + slot * N;
+  __syncthreads();
   auto matvec = [&](const T* mt) {
     C2<T> s = mk<T>(0, 0);
     for (int j = 0; j < N; ++j) { const T m = mt[j * N + i]; s.x = fma(m, my[j].x, s.x); s.y = fma(m, my[j].y, s.y); }
@@ -88,6 +93,8 @@ template <typename T> __global__ void __launch_bounds__(4 * N) project_kernel(co
     }
   }
   if (live) { a.S0[g] = u; a.S0[fs + g] = v; a.S0[2 * fs + g] = w; }
+  __syncthreads();   // vec / red are reused by the next environment
+  }
 }
 
 template <typename T> struct JetArgs {
@@ -319,7 +326,7 @@ template <typename T> struct Impl {
       kc::PArgs<T> p;
       p.c = consts<T>(c); p.B = B; p.jets_on = c.cfg.jets_on; p.S = (const C*)c.S; p.S0 = (C*)c.S0;
       p.M0hat = (const C*)c.M0hat; p.gain = gs[3]; p.dt = (T)dt; p.target = (T)c.cfg.target_bulk_u;
-      kc::project_kernel<T><<<dim3(kc::NAB * kc::NAB, B), 4 * kc::N, kSmemP, s>>>(p);
+      kc::project_kernel<T><<<dim3(kc::NAB * kc::NAB, (B + kc::kEnvsPerCta - 1) / kc::kEnvsPerCta), 4 * kc::N, kSmemP, s>>>(p);
       c.launches += 1;
     }
     return check("rk4_steps");

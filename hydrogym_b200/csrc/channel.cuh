@@ -26,6 +26,7 @@ constexpr int V = N * N * N;
 constexpr int THREADS = 648;  // 72 z-columns x 9 butterfly lanes
 constexpr int NACT = 24;
 constexpr int NAB = 37;
+template <typename T> constexpr int ctas_per_sm() { return sizeof(T) == 4 ? 2 : 1; }
 
 template <typename T> struct C2 { T x, y; };
 template <typename T> __device__ __forceinline__ C2<T> mk(T a, T b) { C2<T> r; r.x = a; r.y = b; return r; }
@@ -43,22 +44,63 @@ template <typename T> __device__ __forceinline__ C2<T> mul_i(C2<T> a) { return m
 __device__ __forceinline__ int wave(int i) { return i < N / 2 ? i : i - N; }
 __device__ __forceinline__ bool kept(int i) { int p = wave(i); return (p < 0 ? -p : p) <= N / 3; }  // U:8-19
 
+// In-register 8-point DFT (radix-2, three stages) and 9-point DFT (3 x 3), exponent sign - (forward) or + (INV).
+template <typename T, bool INV> __device__ __forceinline__ C2<T> rot(C2<T> a) {  // (-i) * a forward, (+i) * a inverse
+  return INV ? mk<T>(-a.y, a.x) : mk<T>(a.y, -a.x);
+}
+template <typename T, bool INV> __device__ __forceinline__ void dft8(C2<T> (&x)[8]) {
+  constexpr T h = T(0.70710678118654752440);
+  const C2<T> a0 = x[0] + x[4], a1 = x[0] - x[4], a2 = x[2] + x[6], a3 = rot<T, INV>(x[2] - x[6]);
+  const C2<T> a4 = x[1] + x[5], a5 = x[1] - x[5], a6 = x[3] + x[7], a7 = rot<T, INV>(x[3] - x[7]);
+  const C2<T> b0 = a0 + a2, b2 = a0 - a2, b1 = a1 + a3, b3 = a1 - a3;
+  const C2<T> b4 = a4 + a6, b6 = rot<T, INV>(a4 - a6), c5 = a5 + a7, c7 = a5 - a7;
+  // W8 * c5 and W8^3 * c7: W8 = (1 -+ i) / sqrt(2), W8^3 = (-1 -+ i) / sqrt(2)
+  const C2<T> b5 = INV ? mk<T>(h * (c5.x - c5.y), h * (c5.x + c5.y)) : mk<T>(h * (c5.x + c5.y), h * (c5.y - c5.x));
+  const C2<T> b7 = INV ? mk<T>(-h * (c7.x + c7.y), h * (c7.x - c7.y)) : mk<T>(h * (c7.y - c7.x), -h * (c7.x + c7.y));
+  x[0] = b0 + b4; x[4] = b0 - b4; x[1] = b1 + b5; x[5] = b1 - b5;
+  x[2] = b2 + b6; x[6] = b2 - b6; x[3] = b3 + b7; x[7] = b3 - b7;
+}
+template <typename T, bool INV> __device__ __forceinline__ void dft3(C2<T>& a, C2<T>& b, C2<T>& c) {
+  constexpr T s3 = T(0.86602540378443864676);
+  const C2<T> s = b + c, d = b - c;
+  const C2<T> t = mk<T>(a.x - T(0.5) * s.x, a.y - T(0.5) * s.y);
+  const C2<T> u = INV ? mk<T>(-s3 * d.y, s3 * d.x) : mk<T>(s3 * d.y, -s3 * d.x);   // (-+ i sqrt(3)/2) * d
+  a = a + s; b = t + u; c = t - u;
+}
+template <typename T, bool INV> __device__ __forceinline__ void dft9(C2<T> (&x)[9]) {
+  constexpr T c1 = T(0.76604444311897803520), s1 = T(0.64278760968653932632);   // cos / sin of 2 pi / 9
+  constexpr T c2 = T(0.17364817766693034885), s2 = T(0.98480775301220805937);   // 4 pi / 9
+  constexpr T c4 = T(-0.93969262078590838405), s4 = T(0.34202014332566873304);  // 8 pi / 9
+  auto tw = [](T c, T s) { return INV ? mk<T>(c, s) : mk<T>(c, -s); };
+  // n = 3 n1 + n2, k = k1 + 3 k2: DFT3 over n1 for each n2, twiddle W9^(n2 k1), DFT3 over n2 for each k1
+  dft3<T, INV>(x[0], x[3], x[6]);
+  dft3<T, INV>(x[1], x[4], x[7]);
+  dft3<T, INV>(x[2], x[5], x[8]);
+  x[4] = cmul(x[4], tw(c1, s1)); x[7] = cmul(x[7], tw(c2, s2));   // n2 = 1: k1 = 1, 2
+  x[5] = cmul(x[5], tw(c2, s2)); x[8] = cmul(x[8], tw(c4, s4));   // n2 = 2: k1 = 1, 2
+  dft3<T, INV>(x[0], x[1], x[2]);   // k1 = 0 -> X[0], X[3], X[6]
+  dft3<T, INV>(x[3], x[4], x[5]);   // k1 = 1 -> X[1], X[4], X[7]
+  dft3<T, INV>(x[6], x[7], x[8]);   // k1 = 2 -> X[2], X[5], X[8]
+  const C2<T> y1 = x[3], y2 = x[6], y3 = x[1], y5 = x[7], y6 = x[2], y7 = x[5];
+  x[1] = y1; x[2] = y2; x[3] = y3; x[5] = y5; x[6] = y6; x[7] = y7;
+}
+
 // Length-72 DFT along the slow axis of a [72][72] shared-memory tile, column z, butterfly lane r (0..8).
 // 72 = 8 x 9: lane r does the 8-point DFT over n1 of x[9 n1 + r] and the twiddle W72^(r k1) (in place: it owns those 8
 // slots), then lanes 0..7 do the 9-point DFT over n2 for k1 = r.  tw[j] = exp(-2 pi i j / 72); INV conjugates.
 // Unnormalised.  Ends with a barrier.
 template <typename T, bool INV> __device__ __forceinline__ void fft72(C2<T>* t, const C2<T>* tw, int z, int r) {
-  auto w = [&](int j) { C2<T> v = tw[j]; if (INV) v.y = -v.y; return v; };
   {
     C2<T> a[8];
 #pragma unroll
     for (int n1 = 0; n1 < 8; ++n1) a[n1] = t[(9 * n1 + r) * N + z];
+    dft8<T, INV>(a);
+    t[r * N + z] = a[0];
 #pragma unroll
-    for (int k1 = 0; k1 < 8; ++k1) {
-      C2<T> s = a[0];
-#pragma unroll
-      for (int n1 = 1; n1 < 8; ++n1) cfma(s, a[n1], w(9 * ((n1 * k1) & 7)));
-      t[(r + 9 * k1) * N + z] = cmul(s, w((r * k1) % N));
+    for (int k1 = 1; k1 < 8; ++k1) {
+      C2<T> w = tw[r * k1];   // r k1 <= 56
+      if (INV) w.y = -w.y;
+      t[(r + 9 * k1) * N + z] = cmul(a[k1], w);
     }
   }
   __syncthreads();
@@ -66,41 +108,53 @@ template <typename T, bool INV> __device__ __forceinline__ void fft72(C2<T>* t, 
   if (r < 8) {
 #pragma unroll
     for (int n2 = 0; n2 < 9; ++n2) b[n2] = t[(n2 + 9 * r) * N + z];
+    dft9<T, INV>(b);
   }
   __syncthreads();
   if (r < 8) {
 #pragma unroll
-    for (int k2 = 0; k2 < 9; ++k2) {
-      C2<T> s = b[0];
-#pragma unroll
-      for (int n2 = 1; n2 < 9; ++n2) cfma(s, b[n2], w(8 * ((n2 * k2) % 9)));
-      t[(r + 8 * k2) * N + z] = s;
-    }
+    for (int k2 = 0; k2 < 9; ++k2) t[(r + 8 * k2) * N + z] = b[k2];
   }
   __syncthreads();
 }
 
 // out[m] = sum_j Mt[j][i] * in[(r + 9 m)][j] for the 8 rows of lane r, column i: a 72 x 72 real matrix (stored
-// transposed) applied along the fast axis of a tile.  `get(row, j)` reads the operand.
-template <typename T, typename Get> __device__ __forceinline__ void zmat_real(const T* Mt, int i, int r, Get get, T (&out)[8]) {
+// transposed, so consecutive i are consecutive words) applied along the fast axis of a [72][72] tile.  The operand is
+// read with 16-byte broadcast loads (4 floats / 2 doubles / 2 complex floats / 1 complex double per load).
+template <typename T> __device__ __forceinline__ void zmat_real(const T* Mt, int i, int r, const T* in, T (&out)[8]) {
+  constexpr int JV = 16 / sizeof(T);
+  struct __align__(16) Vec { T v[JV]; };
 #pragma unroll
   for (int m = 0; m < 8; ++m) out[m] = T(0);
-  for (int j = 0; j < N; ++j) {
-    const T mji = Mt[j * N + i];
+  for (int j = 0; j < N; j += JV) {
+    T mj[JV];
 #pragma unroll
-    for (int m = 0; m < 8; ++m) out[m] = fma(mji, get(r + 9 * m, j), out[m]);
-  }
-}
-template <typename T, typename Get> __device__ __forceinline__ void zmat_cplx(const T* Mt, int i, int r, Get get, C2<T> (&out)[8]) {
-#pragma unroll
-  for (int m = 0; m < 8; ++m) out[m] = mk<T>(T(0), T(0));
-  for (int j = 0; j < N; ++j) {
-    const T mji = Mt[j * N + i];
+    for (int q = 0; q < JV; ++q) mj[q] = Mt[(j + q) * N + i];
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
-      const C2<T> v = get(r + 9 * m, j);
-      out[m].x = fma(mji, v.x, out[m].x);
-      out[m].y = fma(mji, v.y, out[m].y);
+      const Vec v = *reinterpret_cast<const Vec*>(in + (r + 9 * m) * N + j);
+#pragma unroll
+      for (int q = 0; q < JV; ++q) out[m] = fma(mj[q], v.v[q], out[m]);
+    }
+  }
+}
+template <typename T> __device__ __forceinline__ void zmat_cplx(const T* Mt, int i, int r, const C2<T>* in, C2<T> (&out)[8]) {
+  constexpr int JV = 16 / sizeof(C2<T>);
+  struct __align__(16) Vec { C2<T> v[JV]; };
+#pragma unroll
+  for (int m = 0; m < 8; ++m) out[m] = mk<T>(T(0), T(0));
+  for (int j = 0; j < N; j += JV) {
+    T mj[JV];
+#pragma unroll
+    for (int q = 0; q < JV; ++q) mj[q] = Mt[(j + q) * N + i];
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const Vec v = *reinterpret_cast<const Vec*>(in + (r + 9 * m) * N + j);
+#pragma unroll
+      for (int q = 0; q < JV; ++q) {
+        out[m].x = fma(mj[q], v.v[q].x, out[m].x);
+        out[m].y = fma(mj[q], v.v[q].y, out[m].y);
+      }
     }
   }
 }
@@ -139,7 +193,7 @@ template <typename T> struct XArgs {
 };
 
 // grid (3 fields, 72 ky, B), THREADS threads, dynamic smem = 2 tiles + dzzt + twiddles
-template <typename T> __global__ void __launch_bounds__(THREADS, 1) x_kernel(const XArgs<T> a) {
+template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>()) x_kernel(const XArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   C2<T>* t1 = reinterpret_cast<C2<T>*>(smem_raw);
   C2<T>* t2 = t1 + NN;
@@ -203,7 +257,7 @@ template <typename T> __global__ void __launch_bounds__(THREADS, 1) x_kernel(con
     }
     __syncthreads();
     C2<T> visc[8];
-    zmat_cplx<T>(mt, z, r, [&](int row, int j) { return t2[row * N + j]; }, visc);
+    zmat_cplx<T>(mt, z, r, t2, visc);
     __syncthreads();  // t2 is overwritten below
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
@@ -258,7 +312,7 @@ template <typename T> struct YArgs {
 };
 
 // Y1: grid (3 fields, 72 x, B).  Inverse y-transforms (two real fields per complex transform), walls, d/dz.
-template <typename T> __global__ void __launch_bounds__(THREADS, 1) y1_kernel(const YArgs<T> a) {
+template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>()) y1_kernel(const YArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   C2<T>* t1 = reinterpret_cast<C2<T>*>(smem_raw);
   C2<T>* t2 = t1 + NN;
@@ -313,7 +367,7 @@ template <typename T> __global__ void __launch_bounds__(THREADS, 1) y1_kernel(co
   for (int m = 0; m < 8; ++m) fr[(r + 9 * m) * N + z] = fv[m];
   __syncthreads();
   T fz[8];
-  zmat_real<T>(mt, z, r, [&](int row, int j) { return fr[row * N + j]; }, fz);
+  zmat_real<T>(mt, z, r, fr, fz);
   T* out = a.F + ((size_t)f * 4 * a.B + b) * V + (size_t)xi * NN;
   const size_t fs = (size_t)a.B * V;
 #pragma unroll
@@ -324,7 +378,7 @@ template <typename T> __global__ void __launch_bounds__(THREADS, 1) y1_kernel(co
 }
 
 // Y2: grid (3 fields, 72 x, B).  Advective product of field f (C:262-264) or the stored physical field, forward in y.
-template <typename T> __global__ void __launch_bounds__(THREADS, 1) y2_kernel(const YArgs<T> a) {
+template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>()) y2_kernel(const YArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   C2<T>* t1 = reinterpret_cast<C2<T>*>(smem_raw);
   C2<T>* tw = t1 + NN;
