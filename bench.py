@@ -13,7 +13,9 @@ under fresh random actions -- the first env-step of an episode -- which stays fi
                   arithmetic, labelled as such;
   extra.configs : BASELINE.json configs[1..3] at reduced horizons (256^2 fp64, 128^2 x 1024 fp32, 1024^2 x 16 fp32);
   extra.slab    : configs[4], ONE 8192^2 flow slab-decomposed over the N ranks (NCCL all-to-all / peer stores), with a
-                  parity check of both exchanges against the batched kernels.
+                  parity check of both exchanges against the batched kernels;
+  extra.channel : SURVEY 8(f)-4, the 3-D channel-flow env step (72^3, 50 RK4 + projection steps), fp32 / fp64, 1 and 16
+                  envs per GPU, one fp64 env step checked against the reference-source fixture, NumPy oracle timed beside.
 Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement" for the definitions.
 """
 from __future__ import annotations
@@ -509,6 +511,73 @@ def slab_record(torch, dist, args, dev, rank, world, max_over_ranks, peak):
     return rec
 
 
+def channel_record(torch, args, dev, rank, world, max_over_ranks, peak):
+    """the 3-D channel-flow env step (72^3, 50 RK4 + projection steps per env step), env batch sharded
+    over the ranks like the headline.  One fp64 env step is checked against the reference-source fixture first."""
+    import numpy as np
+
+    from hydrogym_b200 import ChannelStepper, channel_constants as cc
+    fields = cc.synthetic_initial_fields(np.float64)
+    rec = {"grid": [72, 72, 72], "rk4_steps_per_env_step": 50, "dt": 2e-4,
+           "initial_state": "synthetic (channel_constants.synthetic_initial_fields): the HF-hosted fields are not "
+                            "reachable offline"}
+    gold_path = os.path.join(ROOT, "tests", "golden", "reference_shim_channel.npz")
+    if os.path.exists(gold_path):
+        gold = np.load(gold_path)
+        st = ChannelStepper(num_envs=1, dtype=torch.float64, device=dev)
+        st.set_state(*[torch.from_numpy(f) for f in fields])
+        obs, rew = st.step(torch.from_numpy(gold["action"]), 0.0, nsteps=50, dt=2e-4)
+        err_o = float(np.linalg.norm(obs[0].cpu().numpy() - gold["step1_obs"]) / np.linalg.norm(gold["step1_obs"]))
+        err_r = abs(float(rew[0]) - float(gold["step1_reward"])) / abs(float(gold["step1_reward"]))
+        st.close()
+        rec["check"] = {"against": "reference source over NumPy stand-ins, fp64, one env step (fixture)",
+                        "rel_err_obs": max_over_ranks(err_o), "rel_err_reward": max_over_ranks(err_r)}
+        rec["check"]["pass"] = bool(rec["check"]["rel_err_obs"] < 1e-9 and rec["check"]["rel_err_reward"] < 1e-9)
+    # algorithmic traffic of the pass structure (DESIGN.md section 7b): complex 72^3 arrays moved per solver step and env
+    arrays = 198.0
+    rec["configs"] = []
+    for dn, B, steps in (("fp32", 1, 3), ("fp32", 16, 2), ("fp64", 1, 2), ("fp64", 16, 1)):
+        dt_ = torch.float32 if dn == "fp32" else torch.float64
+        st = ChannelStepper(num_envs=B, dtype=dt_, device=dev)
+        U, V, W = (torch.from_numpy(f).to(dev, dt_).unsqueeze(0).expand(B, 72, 72, 72).contiguous() for f in fields)
+        st.set_state(U, V, W)
+        act = torch.from_numpy(np.random.default_rng(rank).uniform(-1, 1, (B, 24))).to(dev, dt_)
+        st.step(act, 0.0)
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = st.launch_count
+        e0.record(torch.cuda.current_stream(dev))
+        for i in range(steps):
+            obs, rew = st.step(act, 0.0)   # every step at the start of an episode's clock (jet gain ramp 0 -> 0.3)
+        e1.record(torch.cuda.current_stream(dev))
+        torch.cuda.synchronize(dev)
+        ms = max_over_ranks(e0.elapsed_time(e1) / steps)
+        nbytes = arrays * 72 ** 3 * (8 if dn == "fp32" else 16) * 50 * B
+        rec["configs"].append({"dtype": dn, "envs_per_gpu": B, "ms_per_env_step": ms,
+                               "env_steps_per_s": world * B * 1e3 / ms, "us_per_rk4_step_per_env": 1e3 * ms / 50 / B,
+                               "gpu_launches_per_env_step": int((st.launch_count - l0) // steps),
+                               "frac_of_hbm_roofline": nbytes / (ms * 1e-3) / 1e9 / peak,
+                               "finite": bool(torch.isfinite(obs).all() and torch.isfinite(rew).all())})
+        st.close()
+    if world == 1 and not args.no_cpu_baseline:
+        # CPU leg: the NumPy oracle's RungeKutta4.rk4_step on this box's host cores (one process, NumPy threads)
+        import time
+
+        from oracle import channel_oracle as orc
+        env = orc.ChannelFlowSpectralEnv(initial_fields=fields)
+        s = env.equation.to_spectral(orc.VelocityState(*fields))
+        a = np.zeros(24)
+        s = env.integrator.rk4_step(s, dt=orc.DT, action=a, t=0, fx=2.0)
+        t0 = time.perf_counter()
+        n = 3
+        for i in range(n):
+            s = env.integrator.rk4_step(s, dt=orc.DT, action=a, t=1 + i, fx=2.0)
+        sec = (time.perf_counter() - t0) / n
+        rec["cpu_baseline"] = {"kind": "port", "sample": f"{n} RK4 solver steps of one env (oracle/channel_oracle.py, fp64)",
+                               "s_per_rk4_step": sec, "value": 1.0 / (50 * sec), "unit": "env-steps/s", "cores": 1}
+    return rec
+
+
 def run_native(args):
     import torch
     import torch.distributed as dist
@@ -670,6 +739,11 @@ def run_native(args):
             extra["slab"] = slab_record(torch, dist, args, dev, rank, world, max_over_ranks, peak)
         except Exception as e:
             extra["slab_error"] = f"{type(e).__name__}: {e}"
+        log("extra.channel")
+        try:
+            extra["channel"] = channel_record(torch, args, dev, rank, world, max_over_ranks, peak)
+        except Exception as e:
+            extra["channel_error"] = f"{type(e).__name__}: {e}"
 
     if rank == 0:
         ws = 7 * C * chunk * lanes

@@ -89,3 +89,20 @@ def operators():
 def probe_indices(n=N, m=8):
     """C:69-73."""
     return np.linspace(0, n - 1, m).astype(np.int64)
+
+
+def synthetic_initial_fields(dtype=np.float64):
+    """Deterministic stand-in for the HF-hosted ``Channel_3D_Retau180/initial_field/{U,V,W}.npy`` (C:446-455; not
+    reachable offline): a flat turbulent-like mean profile with grid mean 8 plus smooth O(0.5) three-dimensional
+    perturbations that vanish at the walls.  The bench and the examples use it; real runs pass
+    ``env_config["initial_field_dir"]``."""
+    z = chebyshev_operators()[0]
+    x = np.arange(N) * LX / N
+    y = np.arange(N) * LY / N
+    X, Y, Z = np.meshgrid(x, y, z, indexing="ij")
+    env = 1.0 - Z ** 2
+    prof = 1.0 - Z ** 8
+    U = 8.0 * prof / prof.mean() + 0.6 * env * np.sin(2 * X) * np.cos(2 * Y) * np.cos(0.5 * np.pi * Z)
+    V = 0.5 * env * np.cos(X + 2 * Y) * (1.0 + Z)
+    W = 0.3 * env ** 2 * np.sin(3 * X) * np.sin(2 * Y)
+    return U.astype(dtype), V.astype(dtype), W.astype(dtype)

@@ -71,6 +71,12 @@ def test_product_host_constants_match_reference(gold):
     assert list(cc.probe_indices()) == [0, 10, 20, 30, 40, 50, 60, 71]
 
 
+def test_product_synthetic_fields_are_the_fixture_fields():
+    from hydrogym_b200 import channel_constants as cc
+    for a, b in zip(cc.synthetic_initial_fields(), orc.synthetic_initial_fields()):
+        assert np.array_equal(a, b)
+
+
 def test_rhs_terms_match_reference(gold, env):
     eq = env.equation
     s0 = eq.to_spectral(orc.VelocityState(env.U0, env.V0, env.W0))
