@@ -23,7 +23,8 @@ namespace kc {
 constexpr int N = 72;
 constexpr int NN = N * N;
 constexpr int V = N * N * N;
-constexpr int THREADS = 648;  // 72 z-columns x 9 butterfly lanes
+constexpr int ZP = N / 2;       // each thread owns two adjacent z-columns (16-byte accesses in fp32)
+constexpr int THREADS = ZP * 9;  // 36 column pairs x 9 butterfly lanes
 constexpr int NACT = 24;
 constexpr int NAB = 37;
 template <typename T> constexpr int ctas_per_sm() { return sizeof(T) == 4 ? 2 : 1; }
@@ -85,75 +86,94 @@ template <typename T, bool INV> __device__ __forceinline__ void dft9(C2<T> (&x)[
   x[1] = y1; x[2] = y2; x[3] = y3; x[5] = y5; x[6] = y6; x[7] = y7;
 }
 
-// Length-72 DFT along the slow axis of a [72][72] shared-memory tile, column z, butterfly lane r (0..8).
-// 72 = 8 x 9: lane r does the 8-point DFT over n1 of x[9 n1 + r] and the twiddle W72^(r k1) (in place: it owns those 8
-// slots), then lanes 0..7 do the 9-point DFT over n2 for k1 = r.  tw[j] = exp(-2 pi i j / 72); INV conjugates.
+// two adjacent z-columns of a tile row / global row, moved as one vector
+template <typename E> struct __align__(2 * sizeof(E)) Two { E a, b; };
+template <typename E> __device__ __forceinline__ Two<E> ld2(const E* p) { return *reinterpret_cast<const Two<E>*>(p); }
+template <typename E> __device__ __forceinline__ void st2(E* p, E a, E b) { Two<E> v; v.a = a; v.b = b; *reinterpret_cast<Two<E>*>(p) = v; }
+
+// Length-72 DFT along the slow axis of a [72][72] shared-memory tile, for the two columns z0, z0 + 1, butterfly lane r
+// (0..8).  72 = 8 x 9: lane r does the 8-point DFT over n1 of x[9 n1 + r] and the twiddle W72^(r k1) (in place: it owns
+// those 8 slots), then lanes 0..7 do the 9-point DFT over n2 for k1 = r.  tw[j] = exp(-2 pi i j / 72); INV conjugates.
 // Unnormalised.  Ends with a barrier.
-template <typename T, bool INV> __device__ __forceinline__ void fft72(C2<T>* t, const C2<T>* tw, int z, int r) {
+template <typename T, bool INV> __device__ __forceinline__ void fft72(C2<T>* t, const C2<T>* tw, int z0, int r) {
   {
-    C2<T> a[8];
+    C2<T> a[2][8];
 #pragma unroll
-    for (int n1 = 0; n1 < 8; ++n1) a[n1] = t[(9 * n1 + r) * N + z];
-    dft8<T, INV>(a);
-    t[r * N + z] = a[0];
+    for (int n1 = 0; n1 < 8; ++n1) {
+      const Two<C2<T>> v = ld2(t + (9 * n1 + r) * N + z0);
+      a[0][n1] = v.a; a[1][n1] = v.b;
+    }
+    dft8<T, INV>(a[0]);
+    dft8<T, INV>(a[1]);
+    st2(t + r * N + z0, a[0][0], a[1][0]);
 #pragma unroll
     for (int k1 = 1; k1 < 8; ++k1) {
       C2<T> w = tw[r * k1];   // r k1 <= 56
       if (INV) w.y = -w.y;
-      t[(r + 9 * k1) * N + z] = cmul(a[k1], w);
+      st2(t + (r + 9 * k1) * N + z0, cmul(a[0][k1], w), cmul(a[1][k1], w));
     }
   }
   __syncthreads();
-  C2<T> b[9];
+  C2<T> b[2][9];
   if (r < 8) {
 #pragma unroll
-    for (int n2 = 0; n2 < 9; ++n2) b[n2] = t[(n2 + 9 * r) * N + z];
-    dft9<T, INV>(b);
+    for (int n2 = 0; n2 < 9; ++n2) {
+      const Two<C2<T>> v = ld2(t + (n2 + 9 * r) * N + z0);
+      b[0][n2] = v.a; b[1][n2] = v.b;
+    }
+    dft9<T, INV>(b[0]);
+    dft9<T, INV>(b[1]);
   }
   __syncthreads();
   if (r < 8) {
 #pragma unroll
-    for (int k2 = 0; k2 < 9; ++k2) t[(r + 8 * k2) * N + z] = b[k2];
+    for (int k2 = 0; k2 < 9; ++k2) st2(t + (r + 8 * k2) * N + z0, b[0][k2], b[1][k2]);
   }
   __syncthreads();
 }
 
-// out[m] = sum_j Mt[j][i] * in[(r + 9 m)][j] for the 8 rows of lane r, column i: a 72 x 72 real matrix (stored
-// transposed, so consecutive i are consecutive words) applied along the fast axis of a [72][72] tile.  The operand is
-// read with 16-byte broadcast loads (4 floats / 2 doubles / 2 complex floats / 1 complex double per load).
-template <typename T> __device__ __forceinline__ void zmat_real(const T* Mt, int i, int r, const T* in, T (&out)[8]) {
+// out[c][m] = sum_j Mt[j][i0 + c] * in[(r + 9 m)][j] for the 8 rows of lane r and the two columns i0, i0 + 1: a 72 x 72
+// real matrix (stored transposed, so consecutive i are consecutive words) applied along the fast axis of a [72][72]
+// tile.  The operand is read with 16-byte broadcast loads (4 floats / 2 doubles / 2 complex floats / 1 complex double),
+// the matrix as pairs: 10 shared-memory instructions per 64 (fp32 complex) multiply-adds.
+template <typename T> __device__ __forceinline__ void zmat_real(const T* Mt, int i0, int r, const T* in, T (&out)[2][8]) {
   constexpr int JV = 16 / sizeof(T);
   struct __align__(16) Vec { T v[JV]; };
 #pragma unroll
-  for (int m = 0; m < 8; ++m) out[m] = T(0);
+  for (int m = 0; m < 8; ++m) { out[0][m] = T(0); out[1][m] = T(0); }
   for (int j = 0; j < N; j += JV) {
-    T mj[JV];
+    Two<T> mj[JV];
 #pragma unroll
-    for (int q = 0; q < JV; ++q) mj[q] = Mt[(j + q) * N + i];
-#pragma unroll
-    for (int m = 0; m < 8; ++m) {
-      const Vec v = *reinterpret_cast<const Vec*>(in + (r + 9 * m) * N + j);
-#pragma unroll
-      for (int q = 0; q < JV; ++q) out[m] = fma(mj[q], v.v[q], out[m]);
-    }
-  }
-}
-template <typename T> __device__ __forceinline__ void zmat_cplx(const T* Mt, int i, int r, const C2<T>* in, C2<T> (&out)[8]) {
-  constexpr int JV = 16 / sizeof(C2<T>);
-  struct __align__(16) Vec { C2<T> v[JV]; };
-#pragma unroll
-  for (int m = 0; m < 8; ++m) out[m] = mk<T>(T(0), T(0));
-  for (int j = 0; j < N; j += JV) {
-    T mj[JV];
-#pragma unroll
-    for (int q = 0; q < JV; ++q) mj[q] = Mt[(j + q) * N + i];
+    for (int q = 0; q < JV; ++q) mj[q] = ld2(Mt + (j + q) * N + i0);
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
       const Vec v = *reinterpret_cast<const Vec*>(in + (r + 9 * m) * N + j);
 #pragma unroll
       for (int q = 0; q < JV; ++q) {
-        out[m].x = fma(mj[q], v.v[q].x, out[m].x);
-        out[m].y = fma(mj[q], v.v[q].y, out[m].y);
+        out[0][m] = fma(mj[q].a, v.v[q], out[0][m]);
+        out[1][m] = fma(mj[q].b, v.v[q], out[1][m]);
+      }
+    }
+  }
+}
+template <typename T> __device__ __forceinline__ void zmat_cplx(const T* Mt, int i0, int r, const C2<T>* in, C2<T> (&out)[2][8]) {
+  constexpr int JV = 16 / sizeof(C2<T>);
+  struct __align__(16) Vec { C2<T> v[JV]; };
+#pragma unroll
+  for (int m = 0; m < 8; ++m) { out[0][m] = mk<T>(T(0), T(0)); out[1][m] = out[0][m]; }
+  for (int j = 0; j < N; j += JV) {
+    Two<T> mj[JV];
+#pragma unroll
+    for (int q = 0; q < JV; ++q) mj[q] = ld2(Mt + (j + q) * N + i0);
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const Vec v = *reinterpret_cast<const Vec*>(in + (r + 9 * m) * N + j);
+#pragma unroll
+      for (int q = 0; q < JV; ++q) {
+        out[0][m].x = fma(mj[q].a, v.v[q].x, out[0][m].x);
+        out[0][m].y = fma(mj[q].a, v.v[q].y, out[0][m].y);
+        out[1][m].x = fma(mj[q].b, v.v[q].x, out[1][m].x);
+        out[1][m].y = fma(mj[q].b, v.v[q].y, out[1][m].y);
       }
     }
   }
@@ -192,15 +212,31 @@ template <typename T> struct XArgs {
   T dt6;             // kXLast: S = S0 + dt6 * (ACC + k)
 };
 
+// copy a tile between global memory (row stride `gs` elements) and shared memory, two columns per access
+template <typename E> __device__ __forceinline__ void tile_load(E* t, const E* g, size_t gs, int z0, int r) {
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const Two<E> v = ld2(g + (size_t)(r + 9 * m) * gs + z0);
+    st2(t + (r + 9 * m) * N + z0, v.a, v.b);
+  }
+}
+template <typename E> __device__ __forceinline__ void tile_store(E* g, const E* t, size_t gs, int z0, int r) {
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const Two<E> v = ld2(t + (r + 9 * m) * N + z0);
+    st2(g + (size_t)(r + 9 * m) * gs + z0, v.a, v.b);
+  }
+}
+
 // grid (3 fields, 72 ky, B), THREADS threads, dynamic smem = 2 tiles + dzzt + twiddles
 template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>()) x_kernel(const XArgs<T> a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  extern __shared__ __align__(32) unsigned char smem_raw[];
   C2<T>* t1 = reinterpret_cast<C2<T>*>(smem_raw);
   C2<T>* t2 = t1 + NN;
   T* mt = reinterpret_cast<T*>(t2 + NN);
   C2<T>* tw = reinterpret_cast<C2<T>*>(mt + NN);
   const int f = blockIdx.x, kyi = blockIdx.y, b = blockIdx.z;
-  const int tid = threadIdx.x, z = tid % N, r = tid / N;
+  const int tid = threadIdx.x, z0 = 2 * (tid % ZP), r = tid / ZP;
   const size_t base = ((size_t)f * a.B + b) * V + (size_t)kyi * N;  // + x * NN + z
   if (tid < N) tw[tid] = a.c.tw[tid];
   if (a.mode == kXMid || a.mode == kXLast)
@@ -208,75 +244,86 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
   const bool my = kept(kyi);
 
   if (a.mode == kXForward) {  // plain forward x-transform of BN into S0 (C:156-161)
-#pragma unroll
-    for (int m = 0; m < 8; ++m) t1[(r + 9 * m) * N + z] = a.BN[base + (size_t)(r + 9 * m) * NN + z];
+    tile_load(t1, a.BN + base, NN, z0, r);
     __syncthreads();
-    fft72<T, false>(t1, tw, z, r);
-#pragma unroll
-    for (int m = 0; m < 8; ++m) a.S0[base + (size_t)(r + 9 * m) * NN + z] = t1[(r + 9 * m) * N + z];
+    fft72<T, false>(t1, tw, z0, r);
+    tile_store(a.S0 + base, t1, NN, z0, r);
     return;
   }
 
   if (a.mode == kXFirst) {
-#pragma unroll
-    for (int m = 0; m < 8; ++m) t1[(r + 9 * m) * N + z] = a.S0[base + (size_t)(r + 9 * m) * NN + z];
+    tile_load(t1, a.S0 + base, NN, z0, r);
     __syncthreads();
   } else {
     // ---- this stage's right-hand side k = N_hat + L (C:243-309) on the tile (kx, z) of mode column ky ----
     const C2<T>* state = a.stage == 0 ? a.S0 : a.S;
-    if (my) {
-#pragma unroll
-      for (int m = 0; m < 8; ++m) t1[(r + 9 * m) * N + z] = a.BN[base + (size_t)(r + 9 * m) * NN + z];
-    }
-#pragma unroll
-    for (int m = 0; m < 8; ++m) t2[(r + 9 * m) * N + z] = state[base + (size_t)(r + 9 * m) * NN + z];
+    if (my) tile_load(t1, a.BN + base, NN, z0, r);
+    tile_load(t2, state + base, NN, z0, r);
     __syncthreads();
-    if (my) fft72<T, false>(t1, tw, z, r);
+    if (my) fft72<T, false>(t1, tw, z0, r);
     // -k2 * state on the UNcorrected state (C:296-299), then the wall planes of the tile are replaced (C:227-241)
     const T kyv = a.c.ky[kyi];
-    C2<T> lin[8];
+    C2<T> lin[2][8];
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
       const int kxi = r + 9 * m;
       const T kxv = a.c.kx[kxi];
       const T k2 = kxv * kxv + kyv * kyv;
-      lin[m] = (-k2) * t2[kxi * N + z];
+      const Two<C2<T>> v = ld2(t2 + kxi * N + z0);
+      lin[0][m] = (-k2) * v.a; lin[1][m] = (-k2) * v.b;
     }
     __syncthreads();
     {
       const T g = a.gain[b];
-      const bool wall = z == 0 || z == N - 1;
-      const bool jet = f == 2 && a.jets_on && z >= 1 && z <= 5;
-      if (wall || jet) {
 #pragma unroll
-        for (int m = 0; m < 8; ++m) {
-          const int kxi = r + 9 * m;
-          t2[kxi * N + z] = wall ? mk<T>(T(0), T(0)) : g * a.M0hat[(size_t)b * NN + kxi * N + kyi];
+      for (int c = 0; c < 2; ++c) {
+        const int z = z0 + c;
+        const bool wall = z == 0 || z == N - 1;
+        const bool jet = f == 2 && a.jets_on && z >= 1 && z <= 5;
+        if (wall || jet) {
+#pragma unroll
+          for (int m = 0; m < 8; ++m) {
+            const int kxi = r + 9 * m;
+            t2[kxi * N + z] = wall ? mk<T>(T(0), T(0)) : g * a.M0hat[(size_t)b * NN + kxi * N + kyi];
+          }
         }
       }
     }
     __syncthreads();
-    C2<T> visc[8];
-    zmat_cplx<T>(mt, z, r, t2, visc);
+    C2<T> visc[2][8];
+    zmat_cplx<T>(mt, z0, r, t2, visc);
     __syncthreads();  // t2 is overwritten below
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
       const int kxi = r + 9 * m;
-      const size_t g = base + (size_t)kxi * NN + z;
-      C2<T> k = a.nu * (lin[m] + visc[m]);
-      if (my && kept(kxi)) k = k - t1[kxi * N + z];           // -fft(N) * dealias (C:279-283)
-      if (f == 0 && kxi == 0 && kyi == 0) k.x += a.force;      // + fft of the uniform body force
-      if (a.RHS) a.RHS[g] = k;
-      const C2<T> s0 = a.S0[g];
-      C2<T> nxt;
-      if (a.mode == kXLast) {
-        nxt = s0 + a.dt6 * (a.ACC[g] + k);                    // S:148-152
-      } else {
-        a.ACC[g] = a.stage == 0 ? a.acc_w * k : a.ACC[g] + a.acc_w * k;
-        nxt = s0 + a.a_dt * k;                                // S:139-146
+      const size_t g = base + (size_t)kxi * NN + z0;
+      const Two<C2<T>> nh = ld2(t1 + kxi * N + z0);
+      const Two<C2<T>> s0 = ld2(a.S0 + g);
+      Two<C2<T>> acc;
+      acc.a = mk<T>(T(0), T(0)); acc.b = acc.a;
+      if (a.mode == kXLast || a.stage != 0) acc = ld2(a.ACC + g);
+      C2<T> nxt[2], kk[2];
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        C2<T> k = a.nu * (lin[c][m] + visc[c][m]);
+        if (my && kept(kxi)) k = k - (c ? nh.b : nh.a);            // -fft(N) * dealias (C:279-283)
+        if (f == 0 && kxi == 0 && kyi == 0) k.x += a.force;        // + fft of the uniform body force
+        kk[c] = k;
+        const C2<T> s0c = c ? s0.b : s0.a;
+        const C2<T> ac = c ? acc.b : acc.a;
+        if (a.mode == kXLast) {
+          nxt[c] = s0c + a.dt6 * (ac + k);                         // S:148-152
+        } else {
+          nxt[c] = s0c + a.a_dt * k;                               // S:139-146
+        }
       }
-      a.S[g] = nxt;
-      t1[kxi * N + z] = nxt;
+      if (a.RHS) st2(a.RHS + g, kk[0], kk[1]);
+      if (a.mode != kXLast) {
+        if (a.stage == 0) st2(a.ACC + g, a.acc_w * kk[0], a.acc_w * kk[1]);
+        else st2(a.ACC + g, acc.a + a.acc_w * kk[0], acc.b + a.acc_w * kk[1]);
+      }
+      st2(a.S + g, nxt[0], nxt[1]);
+      st2(t1 + kxi * N + z0, nxt[0], nxt[1]);
     }
     if (a.mode == kXLast) return;
   }
@@ -285,17 +332,14 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
   for (int m = 0; m < 8; ++m) {
     const int kxi = r + 9 * m;
     const T kxv = kxi == N / 2 ? T(0) : a.c.kx[kxi];   // Hermitian projection of `.real`: Nyquist row of d/dx is zero
-    t2[kxi * N + z] = kxv * mul_i(t1[kxi * N + z]);
+    const Two<C2<T>> v = ld2(t1 + kxi * N + z0);
+    st2(t2 + kxi * N + z0, kxv * mul_i(v.a), kxv * mul_i(v.b));
   }
   __syncthreads();
-  fft72<T, true>(t1, tw, z, r);
-  fft72<T, true>(t2, tw, z, r);
-#pragma unroll
-  for (int m = 0; m < 8; ++m) {
-    const size_t g = base + (size_t)(r + 9 * m) * NN + z;
-    a.A[g] = t1[(r + 9 * m) * N + z];
-    a.AX[g] = t2[(r + 9 * m) * N + z];
-  }
+  fft72<T, true>(t1, tw, z0, r);
+  fft72<T, true>(t2, tw, z0, r);
+  tile_store(a.A + base, t1, NN, z0, r);
+  tile_store(a.AX + base, t2, NN, z0, r);
 }
 
 template <typename T> struct YArgs {
@@ -313,13 +357,13 @@ template <typename T> struct YArgs {
 
 // Y1: grid (3 fields, 72 x, B).  Inverse y-transforms (two real fields per complex transform), walls, d/dz.
 template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>()) y1_kernel(const YArgs<T> a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  extern __shared__ __align__(32) unsigned char smem_raw[];
   C2<T>* t1 = reinterpret_cast<C2<T>*>(smem_raw);
   C2<T>* t2 = t1 + NN;
   T* mt = reinterpret_cast<T*>(t2 + NN);
   C2<T>* tw = reinterpret_cast<C2<T>*>(mt + NN);
   const int f = blockIdx.x, xi = blockIdx.y, b = blockIdx.z;
-  const int tid = threadIdx.x, z = tid % N, r = tid / N;
+  const int tid = threadIdx.x, z0 = 2 * (tid % ZP), r = tid / ZP;
   const size_t base = ((size_t)f * a.B + b) * V + (size_t)xi * NN;  // + y * N + z: one contiguous block
   if (tid < N) tw[tid] = a.c.tw[tid];
   if (a.bc)
@@ -327,83 +371,96 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
 #pragma unroll
   for (int m = 0; m < 8; ++m) {
     const int kyi = r + 9 * m;
-    const C2<T> va = a.A[base + kyi * N + z];
+    const Two<C2<T>> va = ld2(a.A + base + kyi * N + z0);
     if (a.bc) {
-      const C2<T> vx = a.AX[base + kyi * N + z];
-      t1[kyi * N + z] = va + mul_i(vx);               // f + i * df/dx: both real after the transform
+      const Two<C2<T>> vx = ld2(a.AX + base + kyi * N + z0);
+      st2(t1 + kyi * N + z0, va.a + mul_i(vx.a), va.b + mul_i(vx.b));   // f + i * df/dx: both real after the transform
       const T kyv = kyi == N / 2 ? T(0) : a.c.ky[kyi];
-      t2[kyi * N + z] = kyv * mul_i(va);
+      st2(t2 + kyi * N + z0, kyv * mul_i(va.a), kyv * mul_i(va.b));
     } else {
-      t1[kyi * N + z] = va;
+      st2(t1 + kyi * N + z0, va.a, va.b);
     }
   }
   __syncthreads();
-  fft72<T, true>(t1, tw, z, r);
+  fft72<T, true>(t1, tw, z0, r);
   const T sc = T(1) / T(NN);
   if (!a.bc) {  // plain `to_physical` (C:163-168)
 #pragma unroll
-    for (int m = 0; m < 8; ++m) a.phys_out[base + (r + 9 * m) * N + z] = sc * t1[(r + 9 * m) * N + z].x;
+    for (int m = 0; m < 8; ++m) {
+      const Two<C2<T>> v = ld2(t1 + (r + 9 * m) * N + z0);
+      st2(a.phys_out + base + (r + 9 * m) * N + z0, sc * v.a.x, sc * v.b.x);
+    }
     return;
   }
-  fft72<T, true>(t2, tw, z, r);
-  T fv[8], fxv[8], fyv[8];
+  fft72<T, true>(t2, tw, z0, r);
+  T fv[2][8], fxv[2][8], fyv[2][8];
   const T g = a.gain[b];
-  const bool wall = z == 0 || z == N - 1;
-  const bool jet = f == 2 && a.jets_on && z >= 1 && z <= 5;
 #pragma unroll
   for (int m = 0; m < 8; ++m) {
     const int yi = r + 9 * m;
-    const C2<T> c1 = t1[yi * N + z];
-    fv[m] = sc * c1.x; fxv[m] = sc * c1.y; fyv[m] = sc * t2[yi * N + z].x;
-    if (wall) { fv[m] = T(0); fxv[m] = T(0); fyv[m] = T(0); }
-    if (jet) {
-      const size_t q = (size_t)b * NN + xi * N + yi;
-      fv[m] = g * a.M0[q]; fxv[m] = g * a.M0dx[q]; fyv[m] = g * a.M0dy[q];
+    const Two<C2<T>> c1 = ld2(t1 + yi * N + z0), c2 = ld2(t2 + yi * N + z0);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const int z = z0 + c;
+      const bool wall = z == 0 || z == N - 1;
+      const bool jet = f == 2 && a.jets_on && z >= 1 && z <= 5;
+      const C2<T> v1 = c ? c1.b : c1.a, v2 = c ? c2.b : c2.a;
+      fv[c][m] = sc * v1.x; fxv[c][m] = sc * v1.y; fyv[c][m] = sc * v2.x;
+      if (wall) { fv[c][m] = T(0); fxv[c][m] = T(0); fyv[c][m] = T(0); }
+      if (jet) {
+        const size_t q = (size_t)b * NN + xi * N + yi;
+        fv[c][m] = g * a.M0[q]; fxv[c][m] = g * a.M0dx[q]; fyv[c][m] = g * a.M0dy[q];
+      }
     }
   }
   __syncthreads();
   T* fr = reinterpret_cast<T*>(t1);  // wall-corrected field as a real tile for the z-derivative
 #pragma unroll
-  for (int m = 0; m < 8; ++m) fr[(r + 9 * m) * N + z] = fv[m];
+  for (int m = 0; m < 8; ++m) st2(fr + (r + 9 * m) * N + z0, fv[0][m], fv[1][m]);
   __syncthreads();
-  T fz[8];
-  zmat_real<T>(mt, z, r, fr, fz);
+  T fz[2][8];
+  zmat_real<T>(mt, z0, r, fr, fz);
   T* out = a.F + ((size_t)f * 4 * a.B + b) * V + (size_t)xi * NN;
   const size_t fs = (size_t)a.B * V;
 #pragma unroll
   for (int m = 0; m < 8; ++m) {
-    const int o = (r + 9 * m) * N + z;
-    out[o] = fv[m]; out[fs + o] = fxv[m]; out[2 * fs + o] = fyv[m]; out[3 * fs + o] = fz[m];
+    const int o = (r + 9 * m) * N + z0;
+    st2(out + o, fv[0][m], fv[1][m]);
+    st2(out + fs + o, fxv[0][m], fxv[1][m]);
+    st2(out + 2 * fs + o, fyv[0][m], fyv[1][m]);
+    st2(out + 3 * fs + o, fz[0][m], fz[1][m]);
   }
 }
 
 // Y2: grid (3 fields, 72 x, B).  Advective product of field f (C:262-264) or the stored physical field, forward in y.
 template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>()) y2_kernel(const YArgs<T> a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  extern __shared__ __align__(32) unsigned char smem_raw[];
   C2<T>* t1 = reinterpret_cast<C2<T>*>(smem_raw);
   C2<T>* tw = t1 + NN;
   const int f = blockIdx.x, xi = blockIdx.y, b = blockIdx.z;
-  const int tid = threadIdx.x, z = tid % N, r = tid / N;
+  const int tid = threadIdx.x, z0 = 2 * (tid % ZP), r = tid / ZP;
   if (tid < N) tw[tid] = a.c.tw[tid];
   const size_t fs = (size_t)a.B * V;
   const size_t e0 = (size_t)b * V + (size_t)xi * NN;
 #pragma unroll
   for (int m = 0; m < 8; ++m) {
-    const int o = (r + 9 * m) * N + z;
-    T n;
+    const int o = (r + 9 * m) * N + z0;
+    T n0, n1;
     if (a.mode == 1) {
-      n = a.phys[(size_t)f * fs + e0 + o];
+      const Two<T> p = ld2(a.phys + (size_t)f * fs + e0 + o);
+      n0 = p.a; n1 = p.b;
     } else {
       const T* d = a.F + (size_t)f * 4 * fs + e0 + o;
-      n = a.F[e0 + o] * d[fs] + a.F[4 * fs + e0 + o] * d[2 * fs] + a.F[8 * fs + e0 + o] * d[3 * fs];
+      const Two<T> u = ld2(a.F + e0 + o), v = ld2(a.F + 4 * fs + e0 + o), w = ld2(a.F + 8 * fs + e0 + o);
+      const Two<T> dx = ld2(d + fs), dy = ld2(d + 2 * fs), dz = ld2(d + 3 * fs);
+      n0 = u.a * dx.a + v.a * dy.a + w.a * dz.a;
+      n1 = u.b * dx.b + v.b * dy.b + w.b * dz.b;
     }
-    t1[o] = mk<T>(n, T(0));
+    st2(t1 + o, mk<T>(n0, T(0)), mk<T>(n1, T(0)));
   }
   __syncthreads();
-  fft72<T, false>(t1, tw, z, r);
-  const size_t base = (size_t)f * fs + e0;
-#pragma unroll
-  for (int m = 0; m < 8; ++m) a.BN[base + (r + 9 * m) * N + z] = t1[(r + 9 * m) * N + z];
+  fft72<T, false>(t1, tw, z0, r);
+  tile_store(a.BN + (size_t)f * fs + e0, t1, N, z0, r);
 }
 
 }  // namespace kc
