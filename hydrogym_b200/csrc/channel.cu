@@ -26,75 +26,98 @@ template <typename T> struct PArgs {
 };
 
 // Pressure projection C:311-372 + walls + constant-mass-flux shift S:166-183, per (kx, ky) mode along z.
-// grid (37 * 37, ceil(B / kEnvsPerCta)): the CTA of (a, b) = (|kx|, |ky|) loads the shared inverse once and applies it
-// to the (up to 4) modes (+-a, +-b) of kEnvsPerCta environments; 4 x 72 threads: thread (i, slot) owns component i of
-// one mode.
-constexpr int kEnvsPerCta = 8;
-template <typename T> __global__ void __launch_bounds__(4 * N) project_kernel(const PArgs<T> a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  T* ainv = reinterpret_cast<T*>(smem_raw);   // [72][72] transposed
-  T* dzt = ainv + NN;
-  C2<T>* vec = reinterpret_cast<C2<T>*>(dzt + NN);   // [4][72] operand of the current matvec
-  __shared__ double red[N];
+// grid (37 * 37, ceil(B / kEnvsPerCta)): the CTA of (a, b) = (|kx|, |ky|) applies the shared inverse to the (up to 4)
+// modes (+-a, +-b) of kEnvsPerCta environments at once; 4 x 72 threads: thread (i, slot) owns component i of one mode
+// in every environment of the CTA.  The matrices are streamed through L1 (each element is used by the 4 slots), the
+// operand vectors are broadcast from shared memory.
+constexpr int kEnvsPerCta = 4;   // (1 when the batch is smaller)
+template <typename T, int E> __global__ void __launch_bounds__(4 * N) project_kernel(const PArgs<T> a) {
+  __shared__ C2<T> vec[E][4][N];
+  __shared__ double red[E][N];
   const int ia = blockIdx.x / NAB, ib = blockIdx.x % NAB;
   const int tid = threadIdx.x, i = tid % N, slot = tid / N;
-  for (int e = tid; e < NN; e += 4 * N) {
-    ainv[e] = a.c.ainv_t[(size_t)blockIdx.x * NN + e];
-    dzt[e] = a.c.dzt[e];
-  }
+  const T* ainv = a.c.ainv_t + (size_t)blockIdx.x * NN;
+  const T* dzt = a.c.dzt;
   const int sx = slot >> 1, sy = slot & 1;
   const bool live = !(sx && (ia == 0 || ia == N / 2)) && !(sy && (ib == 0 || ib == N / 2));
   const int kxi = sx ? N - ia : ia, kyi = sy ? N - ib : ib;
   const size_t fs = (size_t)a.B * V;
-  const int b_end = min(a.B, (int)(blockIdx.y + 1) * kEnvsPerCta);
-  for (int b = blockIdx.y * kEnvsPerCta; b < b_end; ++b) {
-  const size_t g = (size_t)b * V + ((size_t)kxi * N + kyi) * N + i;
-  C2<T> u = mk<T>(0, 0), v = u, w = u;
-  if (live) { u = a.S[g]; v = a.S[fs + g]; w = a.S[2 * fs + g]; }
-  C2<T>* my = vec + slot * N;
-  __syncthreads();
-  auto matvec = [&](const T* mt) {
-    C2<T> s = mk<T>(0, 0);
-    for (int j = 0; j < N; ++j) { const T m = mt[j * N + i]; s.x = fma(m, my[j].x, s.x); s.y = fma(m, my[j].y, s.y); }
-    return s;
+  const int b0 = blockIdx.y * E, nb = min(E, a.B - b0);
+  const size_t g0 = (size_t)b0 * V + ((size_t)kxi * N + kyi) * N + i;
+  C2<T> u[E], v[E], w[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    u[e] = mk<T>(0, 0); v[e] = u[e]; w[e] = u[e];
+    if (live && e < nb) { u[e] = a.S[g0 + (size_t)e * V]; v[e] = a.S[fs + g0 + (size_t)e * V]; w[e] = a.S[2 * fs + g0 + (size_t)e * V]; }
+  }
+  auto put = [&](const C2<T> (&x)[E]) {
+#pragma unroll
+    for (int e = 0; e < E; ++e) vec[e][slot][i] = x[e];
+  };
+  auto matvec = [&](const T* mt, C2<T> (&out)[E]) {
+#pragma unroll
+    for (int e = 0; e < E; ++e) out[e] = mk<T>(0, 0);
+#pragma unroll 24
+    for (int j = 0; j < N; ++j) {
+      const T m = __ldg(mt + j * N + i);
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        const C2<T> x = vec[e][slot][j];
+        out[e].x = fma(m, x.x, out[e].x);
+        out[e].y = fma(m, x.y, out[e].y);
+      }
+    }
   };
   const T kxv = kxi == N / 2 ? T(0) : a.c.kx[kxi];   // `.real` after the derivative: Nyquist rows drop out
   const T kyv = kyi == N / 2 ? T(0) : a.c.ky[kyi];
-  my[i] = w;
-  __syncthreads();
-  const C2<T> dwdz = matvec(dzt);
-  C2<T> rhs = (T(1) / a.dt) * (kxv * mul_i(u) + kyv * mul_i(v) + dwdz);   // C:316-322
-  if (i == 0 || i == N - 1) rhs = (T(1) / a.dt) * w;                     // C:324-333 Neumann data
-  if (ia == 0 && ib == 0 && i == N / 2) rhs = mk<T>(0, 0);               // C:335-337 mean-pressure pin
-  __syncthreads();
-  my[i] = rhs;
-  __syncthreads();
-  const C2<T> p = matvec(ainv);                                          // C:340
-  __syncthreads();
-  my[i] = p;
-  __syncthreads();
-  const C2<T> dpdz = matvec(dzt);
-  u = u - a.dt * (kxv * mul_i(p));                                       // C:343-344
-  v = v - a.dt * (kyv * mul_i(p));
-  w = w - a.dt * dpdz;                                                   // C:346-349
-  // walls at t + dt (C:351-357)
-  const T gn = a.gain[b];
+  const T idt = T(1) / a.dt;
   const bool wall = i == 0 || i == N - 1;
-  if (wall) { u = mk<T>(0, 0); v = u; w = u; }
-  if (a.jets_on && i >= 1 && i <= 5 && live) w = gn * a.M0hat[(size_t)b * NN + kxi * N + kyi];
+  C2<T> t[E], p[E];
+  put(w);
+  __syncthreads();
+  matvec(dzt, t);                                                          // dw/dz
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    C2<T> rhs = idt * (kxv * mul_i(u[e]) + kyv * mul_i(v[e]) + t[e]);     // C:316-322
+    if (wall) rhs = idt * w[e];                                           // C:324-333 Neumann data
+    if (ia == 0 && ib == 0 && i == N / 2) rhs = mk<T>(0, 0);              // C:335-337 mean-pressure pin
+    t[e] = rhs;
+  }
+  __syncthreads();
+  put(t);
+  __syncthreads();
+  matvec(ainv, p);                                                         // C:340
+  __syncthreads();
+  put(p);
+  __syncthreads();
+  matvec(dzt, t);                                                          // dp/dz
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    u[e] = u[e] - a.dt * (kxv * mul_i(p[e]));                              // C:343-344
+    v[e] = v[e] - a.dt * (kyv * mul_i(p[e]));
+    w[e] = w[e] - a.dt * t[e];                                             // C:346-349
+    if (wall) { u[e] = mk<T>(0, 0); v[e] = u[e]; w[e] = u[e]; }            // walls at t + dt (C:351-357)
+    if (a.jets_on && i >= 1 && i <= 5 && live && e < nb)
+      w[e] = a.gain[b0 + e] * a.M0hat[(size_t)(b0 + e) * NN + kxi * N + kyi];
+  }
   if (ia == 0 && ib == 0) {  // S:166-183: only the mean mode sees the bulk-velocity shift
-    if (slot == 0) red[i] = (double)u.x;
-    __syncthreads();
     if (slot == 0) {
-      double s = 0.0;
-      for (int j = 0; j < N; ++j) s += red[j];
-      const T mean = (T)(s / ((double)NN * N));
-      if (!wall) u.x += (a.target - mean) * T(NN);
+#pragma unroll
+      for (int e = 0; e < E; ++e) red[e][i] = (double)u[e].x;
+    }
+    __syncthreads();
+    if (slot == 0 && !wall) {
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        double s = 0.0;
+        for (int j = 0; j < N; ++j) s += red[e][j];
+        u[e].x += (a.target - (T)(s / ((double)NN * N))) * T(NN);
+      }
     }
   }
-  if (live) { a.S0[g] = u; a.S0[fs + g] = v; a.S0[2 * fs + g] = w; }
-  __syncthreads();   // vec / red are reused by the next environment
-  }
+#pragma unroll
+  for (int e = 0; e < E; ++e)
+    if (live && e < nb) { a.S0[g0 + (size_t)e * V] = u[e]; a.S0[fs + g0 + (size_t)e * V] = v[e]; a.S0[2 * fs + g0 + (size_t)e * V] = w[e]; }
 }
 
 template <typename T> struct JetArgs {
@@ -221,13 +244,11 @@ template <typename T> struct Impl {
   static constexpr size_t kTile = (size_t)kc::NN * sizeof(C);
   static constexpr size_t kSmemX = 2 * kTile + kc::NN * sizeof(T) + kc::N * sizeof(C);
   static constexpr size_t kSmemY2 = kTile + kc::N * sizeof(C);
-  static constexpr size_t kSmemP = 2 * kc::NN * sizeof(T) + 4 * kc::N * sizeof(C);
-
+  
   static int init(kc_ctx&) {
     KC_CUDA(cudaFuncSetAttribute(kc::x_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemX));
     KC_CUDA(cudaFuncSetAttribute(kc::y1_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemX));
     KC_CUDA(cudaFuncSetAttribute(kc::y2_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemY2));
-    KC_CUDA(cudaFuncSetAttribute(kc::project_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemP));
     return 0;
   }
 
@@ -326,7 +347,10 @@ template <typename T> struct Impl {
       kc::PArgs<T> p;
       p.c = consts<T>(c); p.B = B; p.jets_on = c.cfg.jets_on; p.S = (const C*)c.S; p.S0 = (C*)c.S0;
       p.M0hat = (const C*)c.M0hat; p.gain = gs[3]; p.dt = (T)dt; p.target = (T)c.cfg.target_bulk_u;
-      kc::project_kernel<T><<<dim3(kc::NAB * kc::NAB, (B + kc::kEnvsPerCta - 1) / kc::kEnvsPerCta), 4 * kc::N, kSmemP, s>>>(p);
+      if (B >= kc::kEnvsPerCta)
+        kc::project_kernel<T, kc::kEnvsPerCta><<<dim3(kc::NAB * kc::NAB, (B + kc::kEnvsPerCta - 1) / kc::kEnvsPerCta), 4 * kc::N, 0, s>>>(p);
+      else
+        kc::project_kernel<T, 1><<<dim3(kc::NAB * kc::NAB, B), 4 * kc::N, 0, s>>>(p);
       c.launches += 1;
     }
     return check("rk4_steps");

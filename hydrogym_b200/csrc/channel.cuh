@@ -29,7 +29,7 @@ constexpr int NACT = 24;
 constexpr int NAB = 37;
 template <typename T> constexpr int ctas_per_sm() { return sizeof(T) == 4 ? 2 : 1; }
 
-template <typename T> struct C2 { T x, y; };
+template <typename T> struct __align__(2 * sizeof(T)) C2 { T x, y; };
 template <typename T> __device__ __forceinline__ C2<T> mk(T a, T b) { C2<T> r; r.x = a; r.y = b; return r; }
 template <typename T> __device__ __forceinline__ C2<T> operator+(C2<T> a, C2<T> b) { return mk<T>(a.x + b.x, a.y + b.y); }
 template <typename T> __device__ __forceinline__ C2<T> operator-(C2<T> a, C2<T> b) { return mk<T>(a.x - b.x, a.y - b.y); }
@@ -128,6 +128,54 @@ template <typename T, bool INV> __device__ __forceinline__ void fft72(C2<T>* t, 
   if (r < 8) {
 #pragma unroll
     for (int k2 = 0; k2 < 9; ++k2) st2(t + (r + 8 * k2) * N + z0, b[0][k2], b[1][k2]);
+  }
+  __syncthreads();
+}
+
+// The same transform on two tiles at once (stage by stage: 3 barriers instead of 6).
+template <typename T, bool INV> __device__ __forceinline__ void fft72_pair(C2<T>* ta, C2<T>* tb, const C2<T>* tw, int z0, int r) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    C2<T>* t = h ? tb : ta;
+    C2<T> a[2][8];
+#pragma unroll
+    for (int n1 = 0; n1 < 8; ++n1) {
+      const Two<C2<T>> v = ld2(t + (9 * n1 + r) * N + z0);
+      a[0][n1] = v.a; a[1][n1] = v.b;
+    }
+    dft8<T, INV>(a[0]);
+    dft8<T, INV>(a[1]);
+    st2(t + r * N + z0, a[0][0], a[1][0]);
+#pragma unroll
+    for (int k1 = 1; k1 < 8; ++k1) {
+      C2<T> w = tw[r * k1];
+      if (INV) w.y = -w.y;
+      st2(t + (r + 9 * k1) * N + z0, cmul(a[0][k1], w), cmul(a[1][k1], w));
+    }
+  }
+  __syncthreads();
+  C2<T> b[2][2][9];
+  if (r < 8) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      C2<T>* t = h ? tb : ta;
+#pragma unroll
+      for (int n2 = 0; n2 < 9; ++n2) {
+        const Two<C2<T>> v = ld2(t + (n2 + 9 * r) * N + z0);
+        b[h][0][n2] = v.a; b[h][1][n2] = v.b;
+      }
+    }
+  }
+  __syncthreads();
+  if (r < 8) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      C2<T>* t = h ? tb : ta;
+      dft9<T, INV>(b[h][0]);
+      dft9<T, INV>(b[h][1]);
+#pragma unroll
+      for (int k2 = 0; k2 < 9; ++k2) st2(t + (r + 8 * k2) * N + z0, b[h][0][k2], b[h][1][k2]);
+    }
   }
   __syncthreads();
 }
@@ -336,8 +384,7 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
     st2(t2 + kxi * N + z0, kxv * mul_i(v.a), kxv * mul_i(v.b));
   }
   __syncthreads();
-  fft72<T, true>(t1, tw, z0, r);
-  fft72<T, true>(t2, tw, z0, r);
+  fft72_pair<T, true>(t1, t2, tw, z0, r);
   tile_store(a.A + base, t1, NN, z0, r);
   tile_store(a.AX + base, t2, NN, z0, r);
 }
@@ -382,9 +429,9 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
     }
   }
   __syncthreads();
-  fft72<T, true>(t1, tw, z0, r);
   const T sc = T(1) / T(NN);
   if (!a.bc) {  // plain `to_physical` (C:163-168)
+    fft72<T, true>(t1, tw, z0, r);
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
       const Two<C2<T>> v = ld2(t1 + (r + 9 * m) * N + z0);
@@ -392,7 +439,7 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
     }
     return;
   }
-  fft72<T, true>(t2, tw, z0, r);
+  fft72_pair<T, true>(t1, t2, tw, z0, r);
   T fv[2][8], fxv[2][8], fyv[2][8];
   const T g = a.gain[b];
 #pragma unroll
