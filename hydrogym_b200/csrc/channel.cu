@@ -202,6 +202,15 @@ struct kc_ctx {
   void *M0 = nullptr, *M0dx = nullptr, *M0dy = nullptr, *M0hat = nullptr, *gain = nullptr;
   int gain_steps = 0;
   std::vector<char> gain_host;
+  // kc_step replays one CUDA graph of its 700-odd launches (transforms + nsteps solver steps) when the step count
+  // and dt repeat; KC_GRAPH=0 launches directly
+  bool use_graph = true;
+  cudaGraphExec_t graph = nullptr;
+  cudaStream_t own = nullptr;          // the graph runs here, ordered after / before the caller's stream by events
+  cudaEvent_t ev_in = nullptr, ev_out = nullptr;
+  int graph_n = -1;
+  double graph_dt = 0.0;
+  long long graph_launches = 0;
 };
 
 namespace {
@@ -421,6 +430,13 @@ int kc_create(kc_handle* out, const kc_config* cfg) {
   c->w = cfg->dtype == KF_F64 ? 8 : 4;
   const size_t w = c->w, B = cfg->B, V = kc::V, NN = kc::NN;
   c->gain_steps = 4096;
+  if (const char* e = getenv("KC_GRAPH")) c->use_graph = atoi(e) != 0;
+  if (cudaStreamCreateWithFlags(&c->own, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_in, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_out, cudaEventDisableTiming) != cudaSuccess) {
+    kc_destroy(c);
+    return kf_set_error("kc_create: stream / event creation failed");
+  }
   struct { void** p; size_t n; } want[] = {
       {&c->tw, KC_N * 2 * w}, {&c->kx, KC_N * w}, {&c->ky, KC_N * w}, {&c->dzt, NN * w}, {&c->dzzt, NN * w},
       {&c->ainv_t, (size_t)KC_NAB * KC_NAB * NN * w}, {&c->jets, KC_ACTIONS * NN * w}, {&c->jets_dx, KC_ACTIONS * NN * w},
@@ -457,6 +473,10 @@ int kc_destroy(kc_handle h) {
   if (!h) return 0;
   cudaSetDevice(h->cfg.device);
   cudaDeviceSynchronize();
+  if (h->graph) cudaGraphExecDestroy(h->graph);
+  if (h->own) cudaStreamDestroy(h->own);
+  if (h->ev_in) cudaEventDestroy(h->ev_in);
+  if (h->ev_out) cudaEventDestroy(h->ev_out);
   for (void* p : h->allocs) cudaFree(p);
   delete h;
   return 0;
@@ -579,12 +599,48 @@ int kc_step(kc_handle h, const void* actions_dev, const double* time_host, int n
             void* obs_dev, void* reward_dev, void* stream) {
   if (int rc = ready(h, "kc_step")) return rc;
   if (!obs_dev || !reward_dev) return kf_set_error("kc_step: null output");
-  const Ops& o = ops(*h);
+  if (!time_host || nsteps < 0 || !(dt > 0)) return kf_set_error("kc_step: bad argument");
+  if (h->cfg.jets_on && !actions_dev) return kf_set_error("kc_step: actions required when jets_on");
+  kc_ctx& c = *h;
+  const Ops& o = ops(c);
   cudaStream_t s = (cudaStream_t)stream;
-  if (int rc = o.to_spectral(*h, s)) return rc;                                   // C:532
-  if (int rc = kc_rk4_steps(h, actions_dev, time_host, nsteps, dt, lo, hi, stream)) return rc;   // C:534-560
-  if (int rc = o.to_physical(*h, s)) return rc;                                   // C:562-563
-  return o.obs(*h, obs_dev, reward_dev, s);                                       // C:566, 502, 515
+  // per-call inputs first (jet patterns of these actions, gains of these clocks), into fixed device buffers
+  if (c.cfg.jets_on)
+    if (int rc = o.jets(c, actions_dev, lo, hi, s)) return rc;
+  if (int rc = o.gains(c, time_host, nsteps, dt, s)) return rc;
+  auto body = [&](cudaStream_t q) -> int {
+    if (int rc = o.to_spectral(c, q)) return rc;                                  // C:532
+    if (int rc = o.rk4_steps(c, nsteps, dt, q)) return rc;                        // C:534-560
+    return o.to_physical(c, q);                                                   // C:562-563
+  };
+  if (c.use_graph) {
+    cudaStream_t q = c.own;   // the caller's stream may be the legacy default stream, which cannot be captured
+    KC_CUDA(cudaEventRecord(c.ev_in, s));
+    KC_CUDA(cudaStreamWaitEvent(q, c.ev_in, 0));
+    if (!c.graph || c.graph_n != nsteps || c.graph_dt != dt) {
+      if (c.graph) { cudaGraphExecDestroy(c.graph); c.graph = nullptr; }
+      const long long l0 = c.launches;
+      cudaGraph_t g = nullptr;
+      KC_CUDA(cudaStreamBeginCapture(q, cudaStreamCaptureModeThreadLocal));
+      const int rc = body(q);
+      cudaError_t e = cudaStreamEndCapture(q, &g);
+      if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+      if (e != cudaSuccess) return kf_set_error((std::string("kc_step: graph capture: ") + cudaGetErrorString(e)).c_str());
+      e = cudaGraphInstantiate(&c.graph, g, 0);
+      cudaGraphDestroy(g);
+      if (e != cudaSuccess) { c.graph = nullptr; return kf_set_error((std::string("kc_step: graph instantiate: ") + cudaGetErrorString(e)).c_str()); }
+      c.graph_n = nsteps; c.graph_dt = dt; c.graph_launches = c.launches - l0;
+      c.launches = l0;   // captured, not launched yet
+    }
+    KC_CUDA(cudaGraphLaunch(c.graph, q));
+    KC_CUDA(cudaEventRecord(c.ev_out, q));
+    KC_CUDA(cudaStreamWaitEvent(s, c.ev_out, 0));
+    c.launches += c.graph_launches;
+    c.have_spectral = true;
+  } else {
+    if (int rc = body(s)) return rc;
+  }
+  return o.obs(c, obs_dev, reward_dev, s);                                        // C:566, 502, 515
 }
 
 long long kc_launch_count(kc_handle h) { return h ? h->launches : 0; }
