@@ -18,6 +18,9 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cstdint>
+#include <type_traits>
+
 namespace kc {
 
 constexpr int N = 72;
@@ -85,6 +88,17 @@ template <typename T, bool INV> __device__ __forceinline__ void dft9(C2<T> (&x)[
   const C2<T> y1 = x[3], y2 = x[6], y3 = x[1], y5 = x[7], y6 = x[2], y7 = x[5];
   x[1] = y1; x[2] = y2; x[3] = y3; x[5] = y5; x[6] = y6; x[7] = y7;
 }
+
+// asynchronous global -> shared copy of n bytes (multiple of 16, both 16-byte aligned) by the whole CTA, and its wait
+__device__ __forceinline__ void async_copy(void* smem_dst, const void* gmem_src, int nbytes, int tid, int nthreads) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  const char* g = reinterpret_cast<const char*>(gmem_src);
+  for (int o = tid * 16; o < nbytes; o += nthreads * 16)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d + o), "l"(g + o) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void async_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // two adjacent z-columns of a tile row / global row, moved as one vector
 template <typename E> struct __align__(2 * sizeof(E)) Two { E a, b; };
@@ -227,6 +241,97 @@ template <typename T> __device__ __forceinline__ void zmat_cplx(const T* Mt, int
   }
 }
 
+// ---- fp32 z-matrix products on the tensor cores: mma.sync m16n8k8 TF32 with the 3-product split ------------------
+// x = hi + lo with hi = tf32(x), lo = tf32(x - hi); D += a_lo b_hi + a_hi b_lo + a_hi b_hi keeps fp32-level accuracy
+// (the dropped a_lo b_lo term is 2^-22 relative).  A 72 x 72 real matrix times the 144 (re / im rows) x 72 operand of
+// an X tile is 9 x 9 x 9 MMA tiles x 3 products; the FMA version spends half of the kernel's instructions on it.
+__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+  const float rest = x - __uint_as_float(hi);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(rest));
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+// D[rho][i] = sum_j A[rho][j] Mt[j][i] for NT consecutive 8-column tiles starting at tile n_first, one 16-row tile:
+// `aoff(rho)` gives the float offset of A[rho][0] in `A`, `astep` the float stride between consecutive j.
+template <int NT, typename AOff>
+__device__ __forceinline__ void mma_rows(const float* A, AOff aoff, int astep, const float* Mt, int m0, int n_first, int lane,
+                                         float (&d)[NT][4]) {
+  const int g = lane >> 2, t = lane & 3;
+  const int oa = aoff(m0 + g), ob = aoff(m0 + g + 8);
+#pragma unroll
+  for (int n = 0; n < NT; ++n) { d[n][0] = 0.f; d[n][1] = 0.f; d[n][2] = 0.f; d[n][3] = 0.f; }
+  for (int k0 = 0; k0 < N; k0 += 8) {
+    uint32_t ahi[4], alo[4];
+    tf32_split(A[oa + astep * (k0 + t)], ahi[0], alo[0]);
+    tf32_split(A[ob + astep * (k0 + t)], ahi[1], alo[1]);
+    tf32_split(A[oa + astep * (k0 + t + 4)], ahi[2], alo[2]);
+    tf32_split(A[ob + astep * (k0 + t + 4)], ahi[3], alo[3]);
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+      const int col = (n_first + n) * 8 + g;
+      uint32_t bhi[2], blo[2];
+      tf32_split(Mt[(k0 + t) * N + col], bhi[0], blo[0]);
+      tf32_split(Mt[(k0 + t + 4) * N + col], bhi[1], blo[1]);
+      mma_tf32(d[n], alo, bhi);
+      mma_tf32(d[n], ahi, blo);
+      mma_tf32(d[n], ahi, bhi);
+    }
+  }
+}
+// complex X-tile operand in place: t (72 x 72 complex floats) := t * Mt along z.  Two barriers inside; the caller has
+// synchronised the operand.  Rows rho = 2 * row + part (re / im interleaved: 2-way bank conflicts on the A loads only).
+__device__ __forceinline__ void zmat_mma_cplx_inplace(const float* Mt, C2<float>* tile, int tid) {
+  float* A = reinterpret_cast<float*>(tile);
+  const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  auto aoff = [](int rho) { return (rho >> 1) * (2 * N) + (rho & 1); };
+  float d[9][4];
+  if (warp < 9) mma_rows<9>(A, aoff, 2, Mt, warp * 16, 0, lane, d);
+  __syncthreads();
+  if (warp < 9) {
+    const int oa = aoff(warp * 16 + g), ob = aoff(warp * 16 + g + 8);
+#pragma unroll
+    for (int n = 0; n < 9; ++n) {
+      const int c = n * 8 + 2 * t;
+      A[oa + 2 * c] = d[n][0]; A[oa + 2 * (c + 1)] = d[n][1];
+      A[ob + 2 * c] = d[n][2]; A[ob + 2 * (c + 1)] = d[n][3];
+    }
+  }
+  __syncthreads();
+}
+// real Y-tile operand: out[row][i] = sum_j in[row][j] Mt[j][i], rows 0..71 (in / out: float [>= 80][72], distinct).
+// Ten warps: 5 row tiles (the last one half empty) x 2 column halves.  One barrier at the end.
+__device__ __forceinline__ void zmat_mma_real(const float* Mt, const float* in, float* out, int tid) {
+  const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  auto aoff = [](int row) { return row * N; };
+  if (warp < 10) {
+    const int m0 = (warp % 5) * 16, nf = (warp / 5) * 5;
+    float d[5][4];
+    if (nf == 0) {
+      mma_rows<5>(in, aoff, 1, Mt, m0, 0, lane, d);
+    } else {
+      float d4[4][4];
+      mma_rows<4>(in, aoff, 1, Mt, m0, 5, lane, d4);
+#pragma unroll
+      for (int n = 0; n < 4; ++n) { d[n][0] = d4[n][0]; d[n][1] = d4[n][1]; d[n][2] = d4[n][2]; d[n][3] = d4[n][3]; }
+    }
+    const int nt = nf == 0 ? 5 : 4;
+    const int ra = m0 + g, rb = ra + 8;
+#pragma unroll
+    for (int n = 0; n < 5; ++n) {
+      if (n < nt) {
+        const int c = (nf + n) * 8 + 2 * t;
+        if (ra < N) { out[ra * N + c] = d[n][0]; out[ra * N + c + 1] = d[n][1]; }
+        if (rb < N) { out[rb * N + c] = d[n][2]; out[rb * N + c + 1] = d[n][3]; }
+      }
+    }
+  }
+  __syncthreads();
+}
+
 template <typename T> struct Consts {
   const C2<T>* tw;     // [72]
   const T* kx;         // [72] C:114-118
@@ -287,8 +392,16 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
   const int tid = threadIdx.x, z0 = 2 * (tid % ZP), r = tid / ZP;
   const size_t base = ((size_t)f * a.B + b) * V + (size_t)kyi * N;  // + x * NN + z
   if (tid < N) tw[tid] = a.c.tw[tid];
-  if (a.mode == kXMid || a.mode == kXLast)
-    for (int e = tid; e < NN; e += THREADS) mt[e] = a.c.dzzt[e];
+  if (a.mode == kXMid || a.mode == kXLast) {
+    async_copy(mt, a.c.dzzt, NN * (int)sizeof(T), tid, THREADS);   // needed only by the matrix product
+    // the epilogue's operands (base state, accumulator) on their way into L2 while the transforms run
+    constexpr int SEGS = (N * (int)sizeof(C2<T>) + 127) / 128;   // 72 rows x 576 (1152) bytes in 128-byte lines
+    for (int l = tid; l < 2 * N * SEGS; l += THREADS) {
+      const int arr = l / (N * SEGS), row = (l / SEGS) % N, seg = l % SEGS;
+      const C2<T>* p = (arr ? a.ACC : a.S0) + base + (size_t)row * NN;
+      prefetch_l2(reinterpret_cast<const char*>(p) + seg * 128);
+    }
+  }
   const bool my = kept(kyi);
 
   if (a.mode == kXForward) {  // plain forward x-transform of BN into S0 (C:156-161)
@@ -309,18 +422,23 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
     tile_load(t2, state + base, NN, z0, r);
     __syncthreads();
     if (my) fft72<T, false>(t1, tw, z0, r);
-    // -k2 * state on the UNcorrected state (C:296-299), then the wall planes of the tile are replaced (C:227-241)
+    // t1 := -fft(N) * dealias + nu * (-k2 * state) on the UNcorrected state (C:279-283, 296-299; own slots), then the
+    // wall planes of the state tile are replaced (C:227-241) and Dzz is applied along z
     const T kyv = a.c.ky[kyi];
-    C2<T> lin[2][8];
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
       const int kxi = r + 9 * m;
       const T kxv = a.c.kx[kxi];
       const T k2 = kxv * kxv + kyv * kyv;
       const Two<C2<T>> v = ld2(t2 + kxi * N + z0);
-      lin[0][m] = (-k2) * v.a; lin[1][m] = (-k2) * v.b;
+      C2<T> p0 = (-(a.nu * k2)) * v.a, p1 = (-(a.nu * k2)) * v.b;
+      if (my && kept(kxi)) {
+        const Two<C2<T>> nh = ld2(t1 + kxi * N + z0);
+        p0 = p0 - nh.a; p1 = p1 - nh.b;
+      }
+      if (f == 0 && kxi == 0 && kyi == 0) { p0.x += a.force; p1.x += a.force; }   // + fft of the uniform body force
+      st2(t1 + kxi * N + z0, p0, p1);
     }
-    __syncthreads();
     {
       const T g = a.gain[b];
 #pragma unroll
@@ -337,15 +455,25 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
         }
       }
     }
+    async_wait();
     __syncthreads();
     C2<T> visc[2][8];
-    zmat_cplx<T>(mt, z0, r, t2, visc);
+    if constexpr (std::is_same<T, float>::value) {
+      zmat_mma_cplx_inplace(mt, t2, tid);   // tensor cores; t2 := Dzz * state_bc
+#pragma unroll
+      for (int m = 0; m < 8; ++m) {
+        const Two<C2<T>> v = ld2(t2 + (r + 9 * m) * N + z0);
+        visc[0][m] = v.a; visc[1][m] = v.b;
+      }
+    } else {
+      zmat_cplx<T>(mt, z0, r, t2, visc);
+    }
     __syncthreads();  // t2 is overwritten below
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
       const int kxi = r + 9 * m;
       const size_t g = base + (size_t)kxi * NN + z0;
-      const Two<C2<T>> nh = ld2(t1 + kxi * N + z0);
+      const Two<C2<T>> pre = ld2(t1 + kxi * N + z0);
       const Two<C2<T>> s0 = ld2(a.S0 + g);
       Two<C2<T>> acc;
       acc.a = mk<T>(T(0), T(0)); acc.b = acc.a;
@@ -353,9 +481,7 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
       C2<T> nxt[2], kk[2];
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
-        C2<T> k = a.nu * (lin[c][m] + visc[c][m]);
-        if (my && kept(kxi)) k = k - (c ? nh.b : nh.a);            // -fft(N) * dealias (C:279-283)
-        if (f == 0 && kxi == 0 && kyi == 0) k.x += a.force;        // + fft of the uniform body force
+        const C2<T> k = (c ? pre.b : pre.a) + a.nu * visc[c][m];
         kk[c] = k;
         const C2<T> s0c = c ? s0.b : s0.a;
         const C2<T> ac = c ? acc.b : acc.a;
@@ -413,8 +539,7 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
   const int tid = threadIdx.x, z0 = 2 * (tid % ZP), r = tid / ZP;
   const size_t base = ((size_t)f * a.B + b) * V + (size_t)xi * NN;  // + y * N + z: one contiguous block
   if (tid < N) tw[tid] = a.c.tw[tid];
-  if (a.bc)
-    for (int e = tid; e < NN; e += THREADS) mt[e] = a.c.dzt[e];
+  if (a.bc) async_copy(mt, a.c.dzt, NN * (int)sizeof(T), tid, THREADS);   // needed only by the z-derivative
 #pragma unroll
   for (int m = 0; m < 8; ++m) {
     const int kyi = r + 9 * m;
@@ -464,9 +589,20 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
   T* fr = reinterpret_cast<T*>(t1);  // wall-corrected field as a real tile for the z-derivative
 #pragma unroll
   for (int m = 0; m < 8; ++m) st2(fr + (r + 9 * m) * N + z0, fv[0][m], fv[1][m]);
+  async_wait();
   __syncthreads();
   T fz[2][8];
-  zmat_real<T>(mt, z0, r, fr, fz);
+  if constexpr (std::is_same<T, float>::value) {
+    float* dz_out = reinterpret_cast<float*>(t2);   // t2's values are in registers (fyv) by now
+    zmat_mma_real(mt, fr, dz_out, tid);
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const Two<T> v = ld2(dz_out + (r + 9 * m) * N + z0);
+      fz[0][m] = v.a; fz[1][m] = v.b;
+    }
+  } else {
+    zmat_real<T>(mt, z0, r, fr, fz);
+  }
   T* out = a.F + ((size_t)f * 4 * a.B + b) * V + (size_t)xi * NN;
   const size_t fs = (size_t)a.B * V;
 #pragma unroll
