@@ -225,3 +225,22 @@ def test_graph_replay_is_bit_identical_to_direct_launches(fields):
     for a, b in zip(out["0"], out["1"]):
         assert all(np.array_equal(x, y) for x, y in zip(a, b))
     assert np.isfinite(out["1"][-1][2]).all()
+
+
+def test_run_channel_pseudospectral_final_and_trajectory(fields):
+    """C:375-403: the direct-solve helper returns the final fields, or the per-step trajectory whose last entry is
+    that final state; both equal the stepper's own rollout."""
+    from hydrogym_b200 import run_channel_pseudospectral
+    act = torch.from_numpy(0.5 * np.cos(np.arange(24.0)))
+    U, V, W = (torch.from_numpy(f) for f in fields)
+    fin = run_channel_pseudospectral(U, V, W, act, dt=orc.DT, nsteps=3, device="cuda:0")
+    traj = run_channel_pseudospectral(U, V, W, act, dt=orc.DT, nsteps=3, return_trajectory=True, device="cuda:0")
+    assert traj[0].shape == (3, 72, 72, 72)
+    for f, t in zip(fin, traj):
+        assert torch.equal(f, t[-1])
+    st = make_stepper(1)
+    st.set_state(U, V, W)
+    st.step(act, 0.0, nsteps=3, dt=orc.DT)
+    for f, g in zip(fin, st.get_state()):
+        assert torch.equal(f, g[0])
+    st.close()
