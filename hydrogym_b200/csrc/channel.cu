@@ -44,6 +44,8 @@ template <typename T, int E> __global__ void __launch_bounds__(4 * N) project_ke
   const size_t fs = (size_t)a.B * V;
   const int b0 = blockIdx.y * E, nb = min(E, a.B - b0);
   const size_t g0 = (size_t)b0 * V + ((size_t)kxi * N + kyi) * N + i;
+  // this CTA's inverse is needed by the second product only: on its way into L2 / L1 from the start
+  for (int l = tid; l * 128 < NN * (int)sizeof(T); l += 4 * N) prefetch_l2(reinterpret_cast<const char*>(ainv) + l * 128);
   C2<T> u[E], v[E], w[E];
 #pragma unroll
   for (int e = 0; e < E; ++e) {
@@ -57,7 +59,7 @@ template <typename T, int E> __global__ void __launch_bounds__(4 * N) project_ke
   auto matvec = [&](const T* mt, C2<T> (&out)[E]) {
 #pragma unroll
     for (int e = 0; e < E; ++e) out[e] = mk<T>(0, 0);
-#pragma unroll 24
+#pragma unroll (E == 1 ? 72 : 24)
     for (int j = 0; j < N; ++j) {
       const T m = __ldg(mt + j * N + i);
 #pragma unroll
