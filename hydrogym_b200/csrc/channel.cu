@@ -46,6 +46,7 @@ template <typename T, int E> __global__ void __launch_bounds__(4 * N) project_ke
   const size_t g0 = (size_t)b0 * V + ((size_t)kxi * N + kyi) * N + i;
   // this CTA's inverse is needed by the second product only: on its way into L2 / L1 from the start
   for (int l = tid; l * 128 < NN * (int)sizeof(T); l += 4 * N) prefetch_l2(reinterpret_cast<const char*>(ainv) + l * 128);
+  grid_dependency_wait();
   C2<T> u[E], v[E], w[E];
 #pragma unroll
   for (int e = 0; e < E; ++e) {
@@ -207,6 +208,9 @@ struct kc_ctx {
   // kc_step replays one CUDA graph of its 700-odd launches (transforms + nsteps solver steps) when the step count
   // and dt repeat; KC_GRAPH=0 launches directly
   bool use_graph = true;
+  // programmatic dependent launch between the kernels of a step: measured slower in fp32 (268 -> 290 us per solver
+  // step at B = 1: the early-resident waiting CTAs hold one of the two CTA slots of an SM), neutral in fp64: opt-in, KC_PDL=1
+  bool pdl = false;
   cudaGraphExec_t graph = nullptr;
   cudaStream_t own = nullptr;          // the graph runs here, ordered after / before the caller's stream by events
   cudaEvent_t ev_in = nullptr, ev_out = nullptr;
@@ -265,6 +269,20 @@ template <typename T> struct Impl {
 
   static dim3 tiles(const kc_ctx& c) { return dim3(3, kc::N, c.cfg.B); }
 
+  // every kernel of a step waits (griddepcontrol.wait) before its first dependent access, so consecutive launches may
+  // overlap the next kernel's prologue (constants, cp.async of the matrices) with the previous kernel's tail
+  template <typename A> static void launch(kc_ctx& c, void (*kernel)(const A), dim3 grid, int threads, size_t smem,
+                                           cudaStream_t s, const A& args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = c.pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, args);
+    c.launches += 1;
+  }
+
   static kc::XArgs<T> xargs(const kc_ctx& c, int mode, int stage, const T* gain, double dt) {
     kc::XArgs<T> a;
     a.c = consts<T>(c);
@@ -295,18 +313,16 @@ template <typename T> struct Impl {
 
   // physical state -> S0 (C:156-161)
   static int to_spectral(kc_ctx& c, cudaStream_t s) {
-    kc::y2_kernel<T><<<tiles(c), kc::THREADS, kSmemY2, s>>>(yargs(c, nullptr, 0, 1));
-    kc::x_kernel<T><<<tiles(c), kc::THREADS, kSmemX, s>>>(xargs(c, kc::kXForward, 0, nullptr, 0.0));
-    c.launches += 2;
+    launch(c, kc::y2_kernel<T>, tiles(c), kc::THREADS, kSmemY2, s, yargs(c, nullptr, 0, 1));
+    launch(c, kc::x_kernel<T>, tiles(c), kc::THREADS, kSmemX, s, xargs(c, kc::kXForward, 0, nullptr, 0.0));
     c.have_spectral = true;
     return check("to_spectral");
   }
 
   // S0 -> physical state (C:163-168)
   static int to_physical(kc_ctx& c, cudaStream_t s) {
-    kc::x_kernel<T><<<tiles(c), kc::THREADS, kSmemX, s>>>(xargs(c, kc::kXFirst, 0, nullptr, 0.0));
-    kc::y1_kernel<T><<<tiles(c), kc::THREADS, kSmemX, s>>>(yargs(c, nullptr, 0, 0));
-    c.launches += 2;
+    launch(c, kc::x_kernel<T>, tiles(c), kc::THREADS, kSmemX, s, xargs(c, kc::kXFirst, 0, nullptr, 0.0));
+    launch(c, kc::y1_kernel<T>, tiles(c), kc::THREADS, kSmemX, s, yargs(c, nullptr, 0, 0));
     return check("to_physical");
   }
 
@@ -337,9 +353,8 @@ template <typename T> struct Impl {
 
   // one right-hand-side evaluation's physical-space half: Y1 (walls at this stage's time) + Y2
   static void y_passes(kc_ctx& c, const T* gain, cudaStream_t s) {
-    kc::y1_kernel<T><<<tiles(c), kc::THREADS, kSmemX, s>>>(yargs(c, gain, 1, 0));
-    kc::y2_kernel<T><<<tiles(c), kc::THREADS, kSmemY2, s>>>(yargs(c, gain, 0, 0));
-    c.launches += 2;
+    launch(c, kc::y1_kernel<T>, tiles(c), kc::THREADS, kSmemX, s, yargs(c, gain, 1, 0));
+    launch(c, kc::y2_kernel<T>, tiles(c), kc::THREADS, kSmemY2, s, yargs(c, gain, 0, 0));
   }
 
   // S:126-185 x n on S0 (gains already uploaded)
@@ -348,33 +363,29 @@ template <typename T> struct Impl {
     for (int i = 0; i < n; ++i) {
       const T* g = (const T*)c.gain + (size_t)i * 3 * B;
       const T* gs[4] = {g, g + B, g + B, g + 2 * B};   // t, t + dt/2, t + dt/2, t + dt
-      kc::x_kernel<T><<<tiles(c), kc::THREADS, kSmemX, s>>>(xargs(c, kc::kXFirst, 0, gs[0], dt));
-      c.launches += 1;
+      launch(c, kc::x_kernel<T>, tiles(c), kc::THREADS, kSmemX, s, xargs(c, kc::kXFirst, 0, gs[0], dt));
       for (int st = 0; st < 4; ++st) {
         y_passes(c, gs[st], s);
-        kc::x_kernel<T><<<tiles(c), kc::THREADS, kSmemX, s>>>(xargs(c, st == 3 ? kc::kXLast : kc::kXMid, st, gs[st], dt));
-        c.launches += 1;
+        launch(c, kc::x_kernel<T>, tiles(c), kc::THREADS, kSmemX, s, xargs(c, st == 3 ? kc::kXLast : kc::kXMid, st, gs[st], dt));
       }
       kc::PArgs<T> p;
       p.c = consts<T>(c); p.B = B; p.jets_on = c.cfg.jets_on; p.S = (const C*)c.S; p.S0 = (C*)c.S0;
       p.M0hat = (const C*)c.M0hat; p.gain = gs[3]; p.dt = (T)dt; p.target = (T)c.cfg.target_bulk_u;
       if (B >= kc::kEnvsPerCta)
-        kc::project_kernel<T, kc::kEnvsPerCta><<<dim3(kc::NAB * kc::NAB, (B + kc::kEnvsPerCta - 1) / kc::kEnvsPerCta), 4 * kc::N, 0, s>>>(p);
+        launch(c, kc::project_kernel<T, kc::kEnvsPerCta>, dim3(kc::NAB * kc::NAB, (B + kc::kEnvsPerCta - 1) / kc::kEnvsPerCta), 4 * kc::N, 0, s, p);
       else
-        kc::project_kernel<T, 1><<<dim3(kc::NAB * kc::NAB, B), 4 * kc::N, 0, s>>>(p);
-      c.launches += 1;
+        launch(c, kc::project_kernel<T, 1>, dim3(kc::NAB * kc::NAB, B), 4 * kc::N, 0, s, p);
     }
     return check("rk4_steps");
   }
 
   static int rhs(kc_ctx& c, void* out, cudaStream_t s) {
     const T* g = (const T*)c.gain;
-    kc::x_kernel<T><<<tiles(c), kc::THREADS, kSmemX, s>>>(xargs(c, kc::kXFirst, 0, g, 0.0));
+    launch(c, kc::x_kernel<T>, tiles(c), kc::THREADS, kSmemX, s, xargs(c, kc::kXFirst, 0, g, 0.0));
     y_passes(c, g, s);
     kc::XArgs<T> a = xargs(c, kc::kXMid, 0, g, 0.0);
     a.RHS = (C*)out;
-    kc::x_kernel<T><<<tiles(c), kc::THREADS, kSmemX, s>>>(a);
-    c.launches += 2;
+    launch(c, kc::x_kernel<T>, tiles(c), kc::THREADS, kSmemX, s, a);
     return check("rhs");
   }
 
@@ -433,6 +444,7 @@ int kc_create(kc_handle* out, const kc_config* cfg) {
   const size_t w = c->w, B = cfg->B, V = kc::V, NN = kc::NN;
   c->gain_steps = 4096;
   if (const char* e = getenv("KC_GRAPH")) c->use_graph = atoi(e) != 0;
+  if (const char* e = getenv("KC_PDL")) c->pdl = atoi(e) != 0;
   if (cudaStreamCreateWithFlags(&c->own, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_in, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_out, cudaEventDisableTiming) != cudaSuccess) {

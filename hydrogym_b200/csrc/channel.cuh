@@ -98,6 +98,12 @@ __device__ __forceinline__ void async_copy(void* smem_dst, const void* gmem_src,
   asm volatile("cp.async.commit_group;" ::: "memory");
 }
 __device__ __forceinline__ void async_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+// programmatic dependent launch: let the next kernel of the stream start its prologue now; wait for the previous
+// kernel's results (no-ops when the launch does not carry the attribute)
+__device__ __forceinline__ void grid_dependency_wait() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // two adjacent z-columns of a tile row / global row, moved as one vector
@@ -392,8 +398,10 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
   const int tid = threadIdx.x, z0 = 2 * (tid % ZP), r = tid / ZP;
   const size_t base = ((size_t)f * a.B + b) * V + (size_t)kyi * N;  // + x * NN + z
   if (tid < N) tw[tid] = a.c.tw[tid];
-  if (a.mode == kXMid || a.mode == kXLast) {
+  if (a.mode == kXMid || a.mode == kXLast)
     async_copy(mt, a.c.dzzt, NN * (int)sizeof(T), tid, THREADS);   // needed only by the matrix product
+  grid_dependency_wait();
+  if (a.mode == kXMid || a.mode == kXLast) {
     // the epilogue's operands (base state, accumulator) on their way into L2 while the transforms run
     constexpr int SEGS = (N * (int)sizeof(C2<T>) + 127) / 128;   // 72 rows x 576 (1152) bytes in 128-byte lines
     for (int l = tid; l < 2 * N * SEGS; l += THREADS) {
@@ -540,6 +548,7 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
   const size_t base = ((size_t)f * a.B + b) * V + (size_t)xi * NN;  // + y * N + z: one contiguous block
   if (tid < N) tw[tid] = a.c.tw[tid];
   if (a.bc) async_copy(mt, a.c.dzt, NN * (int)sizeof(T), tid, THREADS);   // needed only by the z-derivative
+  grid_dependency_wait();
 #pragma unroll
   for (int m = 0; m < 8; ++m) {
     const int kyi = r + 9 * m;
@@ -623,6 +632,7 @@ template <typename T> __global__ void __launch_bounds__(THREADS, ctas_per_sm<T>(
   const int f = blockIdx.x, xi = blockIdx.y, b = blockIdx.z;
   const int tid = threadIdx.x, z0 = 2 * (tid % ZP), r = tid / ZP;
   if (tid < N) tw[tid] = a.c.tw[tid];
+  grid_dependency_wait();
   const size_t fs = (size_t)a.B * V;
   const size_t e0 = (size_t)b * V + (size_t)xi * NN;
 #pragma unroll
