@@ -15,6 +15,9 @@
 // * only the advective products need physical space: per RK stage one X pass (finish the previous stage's right-hand
 //   side, RK update, inverse x-transforms of the state and of its x-derivative), one Y pass (inverse y-transforms,
 //   two real fields per complex transform, walls, z-derivative) and one Y pass for the products + forward y-transform.
+// * a thread owns two adjacent z-columns (16-byte accesses); in fp32 the 72 x 72 z-matrix products run on the tensor
+//   cores (mma.sync TF32, 3-product hi / lo split), in fp64 on FMAs; the matrices arrive by cp.async and are waited for
+//   only before the product; the epilogue's operands are prefetched into L2 at kernel start.
 #pragma once
 #include <cuda_runtime.h>
 
