@@ -244,3 +244,33 @@ def test_run_channel_pseudospectral_final_and_trajectory(fields):
     for f, g in zip(fin, st.get_state()):
         assert torch.equal(f, g[0])
     st.close()
+
+
+def test_reference_ppo_wrapper_stack_over_the_channel_env(fields):
+    """run_ppo.py:165-172's nesting (LogWrapper, ClipAction, VecEnv, NormalizeVecObservation, NormalizeVecReward) over
+    the channel env: the wrappers' arithmetic (NumPy restatement of env_core.py:449-742) applied to this env's own raw
+    outputs."""
+    from hydrogym_b200 import wrappers as W
+    from hydrogym_b200.envs.channel import ChannelFlowSpectralEnv
+    from oracle import wrappers_oracle as wo
+    B, gamma = 2, 0.99
+    cfg = {"initial_fields": fields, "dtype": "float64", "device": "cuda:0"}
+    env, raw_env = ChannelFlowSpectralEnv(cfg), ChannelFlowSpectralEnv(cfg)
+    params = env.default_params
+    w = W.NormalizeVecReward(W.NormalizeVecObservation(W.VecEnv(W.ClipAction(W.LogWrapper(env)), num_envs=B)), gamma)
+    assert w.name == "ChannelFlowSpectralEnv" and w.num_actions == 24
+    obs, st = w.reset(None, params)
+    robs, rstate = raw_env.reset(None, params, num_envs=B)
+    nobs, rno = wo.normalize_obs_reset(robs.cpu().numpy())
+    assert np.abs(obs.cpu().numpy() - nobs).max() < 1e-7
+    rrw = wo.normalize_reward_reset(B)
+    acts = torch.from_numpy(np.stack([1.4 * np.sin(np.arange(24.0)), -0.3 * np.ones(24)])).cuda()
+    obs, st, r, d, info = w.step(None, st, acts, params)
+    raw_obs, rstate, raw_rew, raw_done, _ = raw_env.step(None, rstate, torch.clamp(acts, -1.0, 1.0), params)
+    nobs, rno = wo.normalize_obs_step(rno, raw_obs.cpu().numpy())
+    nrew, rrw = wo.normalize_reward_step(rrw, raw_rew.cpu().numpy(), raw_done.cpu().numpy().astype(np.float64), gamma)
+    assert np.abs(obs.cpu().numpy() - nobs).max() < 1e-6 * max(1.0, np.abs(nobs).max())
+    assert np.abs(r.cpu().numpy() - nrew).max() < 1e-8 * max(1.0, np.abs(nrew).max())
+    assert int(info["timestep"][0]) == 1 and not bool(d.any())
+    env.close()
+    raw_env.close()
