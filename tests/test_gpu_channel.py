@@ -122,6 +122,16 @@ def test_step_env_matches_reference_source(gold, fields):
             assert rel(sub(f), gold[f"step{i}_{c}_sub"]) < 1e-9, (i, c)
             assert abs(np.linalg.norm(f) - gold[f"step{i}_{c}_norm"]) < 1e-9 * gold[f"step{i}_{c}_norm"]
         assert rel(state.U.cpu().numpy()[:, :, 4], gold[f"step{i}_U_plane4"]) < 1e-9
+        # properties of the scheme that hold at any size: walls exactly at rest, grid-mean streamwise velocity on the
+        # target (S:166-183), the five jet planes of w carry one (x, y) pattern with zero mean (C:194-225)
+        U, V, W = (f.cpu().numpy() for f in (state.U, state.V, state.W))
+        for f in (U, V, W):
+            assert not f[:, :, 0].any() and not f[:, :, -1].any()
+        # the shift is computed before the walls are zeroed again, so 2/72 of each step's (small) shift is lost
+        assert abs(U.mean() - 8.0) < 1e-3
+        for k in range(2, 6):
+            assert np.abs(W[:, :, k] - W[:, :, 1]).max() < 1e-12 * max(1.0, np.abs(W[:, :, 1]).max())
+        assert abs(W[:, :, 1].mean()) < 1e-12
     env.close()
 
 
