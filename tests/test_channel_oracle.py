@@ -102,3 +102,43 @@ def test_jet_gain_ramp():
     g = orc.PseudoSpectralNavierStokes3D.jet_gain
     assert g(0.0) == 0.0 and abs(g(5.0) - 0.15) < 1e-15 and g(20.0) == 0.3
     assert abs(g(45.0) - 0.15) < 1e-15 and abs(g(60.0) + 0.3) < 1e-15   # negative beyond action_time, as the reference
+
+
+def test_pressure_inverses_are_shared_by_the_four_sign_combinations(env):
+    """kc_set_operators uploads 37 x 37 inverses (|kx|, |ky|): k2 is even in both wavenumbers, so the oracle's own
+    72 x 72 inverses (C:128-148) must coincide for (+-kx, +-ky) -- including the Nyquist lines."""
+    from hydrogym_b200 import channel_constants as cc
+    a_inv = cc.operators()[3]
+    A = env.equation.A_inv.reshape(72, 72, 72, 72)
+    rng = np.random.default_rng(0)
+    for kxi, kyi in [(0, 0), (0, 36), (36, 36), (71, 1), (5, 67)] + [tuple(rng.integers(0, 72, 2)) for _ in range(12)]:
+        ia, ib = min(kxi, 72 - kxi), min(kyi, 72 - kyi)
+        assert rel(a_inv[ia, ib], A[kxi, kyi]) < 1e-12, (kxi, kyi)
+
+
+def test_jet_basis_is_linear_and_zero_mean(env):
+    """The kernels combine 24 precomputed patterns linearly (C:194-217 is linear in Vjets): any amplitude vector
+    gives the oracle's plane; each pattern has zero mean and lives on the 6 x 4 lattice of grid indices."""
+    from hydrogym_b200 import channel_constants as cc
+    jets = cc.jet_basis()
+    assert jets.shape == (24, 72, 72) and np.abs(jets.mean(axis=(1, 2))).max() < 1e-15
+    rng = np.random.default_rng(3)
+    for _ in range(3):
+        v = rng.uniform(-2, 2, 24)
+        assert rel(np.tensordot(v, jets, 1), env.equation.jet_pattern(v)) < 1e-13
+    peak = np.unravel_index(np.argmax(jets[0]), (72, 72))
+    assert peak == (3, 4)                       # first slit centre: x index 3, y index 4 (C:199-200)
+    peak = np.unravel_index(np.argmax(jets[23]), (72, 72))
+    assert peak == (44, 67)                     # last: x = int(72 * 2/3) - 4, y = 72 - 5
+
+
+def test_oracle_env_step_bookkeeping(env):
+    """time += 50 regardless of the oracle's shortened rollout, terminal at the horizon, reward = -wss (C:502-505)."""
+    short = orc.ChannelFlowSpectralEnv(nsteps=1)
+    obs, st = short.reset_env()
+    obs, st, reward, done, info = short.step_env(st, np.zeros(24))
+    assert st["time"] == 50 and not done and info["discount"] == 1.0 and obs.shape == (128,)
+    assert reward == -orc.wss_compute(4, st["U"], z=short.equation.z)
+    st["time"] = orc.MAX_STEPS - 50
+    _, st, _, done, info = short.step_env(st, np.zeros(24))
+    assert done and info["discount"] == 0.0
